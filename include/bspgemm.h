@@ -1,0 +1,152 @@
+/*
+ * bspgemm.h -- C ABI of the B200-native block-sparse chain-product library (libbspgemm.so).
+ *
+ * Drop-in boundary for the one hot path of
+ * UmeshK2005/Sparse-Matrix-Multiplication-using-OpenMP-MPI-and-CUDA:
+ *     helper2 -> helper -> matrix_multiplyKernel          (sparse_matrix_mult.cu, "cu:N" below)
+ * i.e. C = A*B on block-sparse matrices of k x k uint64 tiles, and the pairwise-tree product
+ * of a chain of them, with the reference's exact arithmetic:
+ *     acc = ((acc + ((a*b mod 2^64) % (2^64-1))) mod 2^64) % (2^64-1)        (cu:59, cu:61)
+ * folded per output element over the matching tile pairs in ascending inner block index and,
+ * inside a pair, ascending inner element index (cu:54-62, cu:149-155).
+ *
+ * Conventions: plain C types, opaque handles; the caller owns handles, the library owns the
+ * device memory behind them; every call returns a status (0 = BSP_OK), the library never
+ * exits the process (the reference's CUDA_CHECK, cu:33-41, calls exit()).  One context = one
+ * device + one stream; a context is not thread-safe; different contexts may be used from
+ * different host threads.  There is no CPU fallback: without a CUDA device every compute
+ * call fails with BSP_ERR_CUDA.
+ */
+#ifndef BSPGEMM_H
+#define BSPGEMM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bsp_ctx bsp_ctx;
+typedef struct bsp_mat bsp_mat;
+
+enum {
+    BSP_OK = 0,
+    BSP_ERR_ARG = 1,      /* bad argument (null, negative coordinate, k mismatch, ...) */
+    BSP_ERR_CUDA = 2,     /* a CUDA runtime call failed; see bsp_last_error */
+    BSP_ERR_NOMEM = 3,    /* device or host allocation failed */
+    BSP_ERR_LIMIT = 4,    /* a size exceeds what this build supports (stated in the message) */
+    BSP_ERR_IO = 5        /* file could not be read / written / parsed */
+};
+
+/* Per-product counters and device timings (CUDA events on the context's stream). */
+typedef struct bsp_stats {
+    int64_t nnzb_a, nnzb_b, nnzb_c; /* tiles in A, B and C */
+    int64_t nprod;                  /* tile products = sum over A tiles (i,j) of |B row j| */
+    double ms_symbolic;             /* pattern of C + pair lists */
+    double ms_numeric;              /* tile multiply-accumulate */
+    double ms_total;                /* whole call, device time */
+    int64_t launches;               /* kernels launched by this call */
+    int64_t exact_refolds;          /* output elements recomputed with the per-operation path */
+    int32_t numeric_path;           /* which numeric kernel ran: 0 generic, 4 / 8 / 16 / 32 = tile-size specialised */
+    int32_t reserved;
+} bsp_stats;
+
+/* ---- context ------------------------------------------------------------------------ */
+
+/* Replaces the process-wide set-up of main (cu:421-436: the four cudaMalloc'd staging
+ * buffers lent to every helper call).  `stream` is a cudaStream_t to run on, or NULL for a
+ * stream owned by the context. */
+int bsp_ctx_create(int device, void *stream, bsp_ctx **out);
+void bsp_ctx_destroy(bsp_ctx *ctx);                       /* cu:667-675 */
+const char *bsp_last_error(const bsp_ctx *ctx);           /* message of the last failing call */
+int bsp_ctx_sync(bsp_ctx *ctx);                           /* cudaStreamSynchronize */
+int64_t bsp_ctx_launch_count(const bsp_ctx *ctx);         /* kernels launched so far */
+const char *bsp_version(void);
+
+/* ---- matrices (struct one_matrix, cu:26-32) ----------------------------------------- */
+
+/* Upload a coordinate list from HOST memory: brow/bcol [nnzb], vals [nnzb*k*k] tile-major,
+ * each tile row-major.  Keys may be unsorted; on duplicate keys the LAST one wins, as the
+ * reader's m[{row,col}] = v does (cu:383).  Coordinates must be >= 0. */
+int bsp_mat_from_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,
+                     const int32_t *brow, const int32_t *bcol, const uint64_t *vals, bsp_mat **out);
+
+/* Same, from DEVICE memory (arrays are copied, not adopted). */
+int bsp_mat_from_device_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,
+                            const int32_t *d_brow, const int32_t *d_bcol, const uint64_t *d_vals,
+                            bsp_mat **out);
+
+/* Header of a matrix: rows/cols as carried by the reference (cu:280-282), tile edge, tiles. */
+int bsp_mat_info(const bsp_mat *m, int32_t *rows, int32_t *cols, int32_t *k, int64_t *nnzb);
+
+/* Download as a coordinate list sorted by (brow, bcol) -- the iteration order of the
+ * reference's std::map that the writer relies on (cu:598).  Host buffers sized from
+ * bsp_mat_info. */
+int bsp_mat_to_coo(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol, uint64_t *vals);
+
+/* Device view (CSR of blocks) for callers that move partial products between GPUs:
+ * rowptr [nbrows+1] int32, colidx [nnzb] int32, vals [nnzb*k*k] uint64.  Pointers stay
+ * valid until the matrix is freed. */
+int bsp_mat_device_view(const bsp_mat *m, int32_t *nbrows, int32_t *nbcols,
+                        const int32_t **d_rowptr, const int32_t **d_colidx, const uint64_t **d_vals);
+
+/* Build a matrix from a device CSR-of-blocks view (arrays are copied).  The receiving side
+ * of the partial-product exchange that replaces MPI_Recv + map rebuild (cu:513-551). */
+int bsp_mat_from_device_bcsr(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows,
+                             int32_t nbcols, int64_t nnzb, const int32_t *d_rowptr,
+                             const int32_t *d_colidx, const uint64_t *d_vals, bsp_mat **out);
+
+void bsp_mat_free(bsp_ctx *ctx, bsp_mat *m);
+
+/* ---- the hot path ------------------------------------------------------------------- */
+
+/* C = A*B  (= helper, cu:97-286).  A and B are borrowed and not modified; *C is new.
+ * All-zero result tiles are kept, as the reference keeps them in intermediates
+ * (cu:259-269).  stats may be NULL. */
+int bsp_spgemm(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, bsp_mat **C, bsp_stats *stats);
+
+/* Block-row panel [row_lo, row_hi) of C = A*B: the unit of row-panel sharding across GPUs
+ * (no counterpart in the reference, which cannot split one product).  The result has the
+ * full block-row space of A with tiles only in the panel. */
+int bsp_spgemm_panel(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo, int32_t row_hi,
+                     bsp_mat **C, bsp_stats *stats);
+
+/* Product of mats[0..n-1] by the reference's pairwise tree: adjacent pairs at every level,
+ * an odd tail is carried to the next level unchanged (= helper2, cu:287-327).  Inputs are
+ * borrowed; *out is new (a copy of mats[0] when n == 1).  If log is non-NULL it receives the
+ * "multiplying a b\n" lines the reference prints (cu:301), with `log_base` added to the
+ * indices (the sub-chain start index of cu:442/450).  stats (may be NULL) is summed over the
+ * products. */
+int bsp_chain(bsp_ctx *ctx, bsp_mat *const *mats, int32_t n, bsp_mat **out, bsp_stats *stats,
+              char *log, size_t log_cap, int32_t log_base);
+
+/* Remove tiles whose k*k entries are all zero, in place (the intended semantics of
+ * cu:577-592; the shipped loop erases while iterating and crashes). */
+int bsp_prune_zero(bsp_ctx *ctx, bsp_mat *m);
+
+/* One call from host buffers to host buffers: upload A and B, multiply, download C sorted.
+ * The shape of the reference's helper seen from its caller (one_matrix in, one_matrix out).
+ * Pass NULL output arrays to only obtain *nnzb_c (then call again), or call
+ * bsp_multiply_host_alloc. cap_c = capacity of the output arrays in tiles. */
+int bsp_multiply_host(bsp_ctx *ctx, int32_t k,
+                      int32_t rows_a, int32_t cols_a, int64_t nnzb_a, const int32_t *brow_a,
+                      const int32_t *bcol_a, const uint64_t *vals_a,
+                      int32_t rows_b, int32_t cols_b, int64_t nnzb_b, const int32_t *brow_b,
+                      const int32_t *bcol_b, const uint64_t *vals_b,
+                      int64_t cap_c, int64_t *nnzb_c, int32_t *brow_c, int32_t *bcol_c,
+                      uint64_t *vals_c, bsp_stats *stats);
+
+/* ---- text format of the reference (either side of the path) -------------------------- */
+
+/* Parse one "matrixI" file (rows cols / blocks / {brow bcol / k*k values}), cu:345-383. */
+int bsp_mat_read_text(bsp_ctx *ctx, const char *path, int32_t k, bsp_mat **out);
+
+/* Write the output layout of cu:595-608 ("R C", count, then per tile "i j" and k rows of k
+ * values, single spaces, no trailing space, '\n' line ends), tiles in (brow, bcol) order. */
+int bsp_mat_write_text(bsp_ctx *ctx, const bsp_mat *m, const char *path);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BSPGEMM_H */

@@ -1,0 +1,381 @@
+// bsp_capi.cu -- the extern "C" boundary declared in include/bspgemm.h.
+#include <new>
+#include <vector>
+
+#include "bsp_internal.h"
+
+namespace {
+
+bool valid_mat(const bsp_mat *m) { return m && m->rowptr; }
+
+int new_empty_like(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbr, int32_t nbc, bsp_mat **out)
+{
+    bsp_mat *m = new (std::nothrow) bsp_mat();
+    if (!m) BSP_FAIL(ctx, BSP_ERR_NOMEM, "host allocation failed");
+    m->rows = rows; m->cols = cols; m->k = k; m->nbr = nbr; m->nbc = nbc; m->nnzb = 0; m->device = ctx->device;
+    m->rowptr = nullptr; m->colidx = nullptr; m->vals = nullptr;
+    *out = m;
+    return BSP_OK;
+}
+
+void accumulate(bsp_stats *dst, const bsp_stats &s)
+{
+    dst->nnzb_a += s.nnzb_a; dst->nnzb_b += s.nnzb_b; dst->nnzb_c += s.nnzb_c; dst->nprod += s.nprod;
+    dst->ms_symbolic += s.ms_symbolic; dst->ms_numeric += s.ms_numeric; dst->ms_total += s.ms_total;
+    dst->launches += s.launches; dst->exact_refolds += s.exact_refolds;
+    dst->numeric_path = s.numeric_path;
+}
+
+int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo, int32_t row_hi, bsp_mat **C,
+                bsp_stats *stats)
+{
+    if (!ctx || !C) return BSP_ERR_ARG;
+    *C = nullptr;
+    if (!valid_mat(A) || !valid_mat(B)) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm: null matrix");
+    if (A->k != B->k) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm: tile edge differs (%d vs %d)", A->k, B->k);
+    if (A->device != ctx->device || B->device != ctx->device)
+        BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm: matrices live on another device than the context");
+    BSP_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t launches0 = ctx->launches;
+    bsp_stats st;
+    memset(&st, 0, sizeof(st));
+    st.nnzb_a = A->nnzb; st.nnzb_b = B->nnzb;
+
+    bsp_mat *c = nullptr;
+    BSP_TRY(new_empty_like(ctx, A->rows, B->cols, A->k, A->nbr, B->nbc, &c)); // cu:280-282
+    *C = c;
+    BSP_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+    bsp_symbolic_out sym;
+    BSP_TRY(bsp_symbolic(ctx, A, B, row_lo, row_hi, &sym));
+    BSP_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+    c->rowptr = sym.c_rowptr;
+    c->colidx = sym.c_colidx;
+    c->nnzb = sym.nnzb_c;
+    BSP_TRY(bsp_alloc(ctx, &c->vals, (size_t)sym.nnzb_c * A->k * A->k));
+    BSP_TRY(bsp_numeric(ctx, A, B, &sym, c->vals, &st.exact_refolds, &st.numeric_path));
+    BSP_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+    bsp_release(ctx, sym.pair_ptr);
+    bsp_release(ctx, sym.pairs);
+    BSP_CUDA(ctx, cudaEventSynchronize(ctx->ev[2]));
+    float ms01 = 0, ms12 = 0;
+    BSP_CUDA(ctx, cudaEventElapsedTime(&ms01, ctx->ev[0], ctx->ev[1]));
+    BSP_CUDA(ctx, cudaEventElapsedTime(&ms12, ctx->ev[1], ctx->ev[2]));
+    st.nnzb_c = sym.nnzb_c; st.nprod = sym.nprod;
+    st.ms_symbolic = ms01; st.ms_numeric = ms12; st.ms_total = ms01 + ms12;
+    st.launches = ctx->launches - launches0;
+    if (stats) *stats = st;
+    return BSP_OK;
+}
+
+int clone_mat(bsp_ctx *ctx, const bsp_mat *s, bsp_mat **out)
+{
+    bsp_mat *m = nullptr;
+    BSP_TRY(new_empty_like(ctx, s->rows, s->cols, s->k, s->nbr, s->nbc, &m));
+    *out = m;
+    m->nnzb = s->nnzb;
+    const size_t kk = (size_t)s->k * s->k;
+    BSP_TRY(bsp_alloc(ctx, &m->rowptr, (size_t)s->nbr + 1));
+    BSP_TRY(bsp_alloc(ctx, &m->colidx, (size_t)s->nnzb));
+    BSP_TRY(bsp_alloc(ctx, &m->vals, (size_t)s->nnzb * kk));
+    BSP_CUDA(ctx, cudaMemcpyAsync(m->rowptr, s->rowptr, ((size_t)s->nbr + 1) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (s->nnzb) {
+        BSP_CUDA(ctx, cudaMemcpyAsync(m->colidx, s->colidx, (size_t)s->nnzb * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(m->vals, s->vals, (size_t)s->nnzb * kk * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    return BSP_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *bsp_version(void) { return "bspgemm 0.1 (sm_100a)"; }
+
+int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
+{
+    if (!out) return BSP_ERR_ARG;
+    *out = nullptr;
+    bsp_ctx *ctx = new (std::nothrow) bsp_ctx();
+    if (!ctx) return BSP_ERR_NOMEM;
+    memset(ctx, 0, sizeof(*ctx));
+    ctx->device = device;
+    *out = ctx; // returned even on failure so that bsp_last_error can be read; destroy it either way
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        snprintf(ctx->err, sizeof(ctx->err), "no CUDA device available (%s); this library has no CPU fallback",
+                 e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        cudaGetLastError();
+        return BSP_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) BSP_FAIL(ctx, BSP_ERR_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    BSP_CUDA(ctx, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    BSP_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    if (stream) {
+        ctx->stream = (cudaStream_t)stream;
+        ctx->owns_stream = false;
+    } else {
+        BSP_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        ctx->owns_stream = true;
+    }
+    for (int i = 0; i < 4; i++) BSP_CUDA(ctx, cudaEventCreate(&ctx->ev[i]));
+    ctx->pinned_bytes = 4096;
+    BSP_CUDA(ctx, cudaMallocHost(&ctx->pinned, ctx->pinned_bytes));
+    // keep freed blocks in the stream-ordered pool: a chain allocates and frees every product
+    cudaMemPool_t pool;
+    BSP_CUDA(ctx, cudaDeviceGetDefaultMemPool(&pool, device));
+    uint64_t thr = UINT64_MAX;
+    BSP_CUDA(ctx, cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    return BSP_OK;
+}
+
+void bsp_ctx_destroy(bsp_ctx *ctx)
+{
+    if (!ctx) return;
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (int i = 0; i < 4; i++)
+        if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->owns_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *bsp_last_error(const bsp_ctx *ctx) { return ctx ? ctx->err : "null context"; }
+
+int bsp_ctx_sync(bsp_ctx *ctx)
+{
+    if (!ctx) return BSP_ERR_ARG;
+    BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSP_OK;
+}
+
+int64_t bsp_ctx_launch_count(const bsp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int bsp_mat_from_device_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb, const int32_t *d_brow,
+                            const int32_t *d_bcol, const uint64_t *d_vals, bsp_mat **out)
+{
+    if (!ctx || !out) return BSP_ERR_ARG;
+    *out = nullptr;
+    if (k < 1 || nnzb < 0) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_from_device_coo: k=%d nnzb=%lld", k, (long long)nnzb);
+    if (nnzb > 0x7fffffffLL) BSP_FAIL(ctx, BSP_ERR_LIMIT, "more than 2^31-1 tiles");
+    BSP_CUDA(ctx, cudaSetDevice(ctx->device));
+    // coordinate range (device arrays): copy back and scan on the host -- ingest is not the hot path
+    int32_t max_row = -1, max_col = -1;
+    if (nnzb > 0) {
+        std::vector<int32_t> hr((size_t)nnzb), hc((size_t)nnzb);
+        BSP_CUDA(ctx, cudaMemcpyAsync(hr.data(), d_brow, (size_t)nnzb * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(hc.data(), d_bcol, (size_t)nnzb * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        for (int64_t i = 0; i < nnzb; i++) {
+            if (hr[i] < 0 || hc[i] < 0) BSP_FAIL(ctx, BSP_ERR_ARG, "negative block coordinate at entry %lld", (long long)i);
+            if (hr[i] > max_row) max_row = hr[i];
+            if (hc[i] > max_col) max_col = hc[i];
+        }
+    }
+    return bsp_ingest_coo(ctx, rows, cols, k, nnzb, d_brow, d_bcol, d_vals, max_row, max_col, out);
+}
+
+int bsp_mat_from_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb, const int32_t *brow,
+                     const int32_t *bcol, const uint64_t *vals, bsp_mat **out)
+{
+    if (!ctx || !out) return BSP_ERR_ARG;
+    *out = nullptr;
+    if (k < 1 || nnzb < 0 || (nnzb > 0 && (!brow || !bcol || !vals)))
+        BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_from_coo: bad arguments (k=%d nnzb=%lld)", k, (long long)nnzb);
+    if (nnzb > 0x7fffffffLL) BSP_FAIL(ctx, BSP_ERR_LIMIT, "more than 2^31-1 tiles");
+    BSP_CUDA(ctx, cudaSetDevice(ctx->device));
+    int32_t max_row = -1, max_col = -1;
+    for (int64_t i = 0; i < nnzb; i++) {
+        if (brow[i] < 0 || bcol[i] < 0) BSP_FAIL(ctx, BSP_ERR_ARG, "negative block coordinate at entry %lld", (long long)i);
+        if (brow[i] > max_row) max_row = brow[i];
+        if (bcol[i] > max_col) max_col = bcol[i];
+    }
+    const size_t kk = (size_t)k * k;
+    int32_t *d_r = nullptr, *d_c = nullptr;
+    uint64_t *d_v = nullptr;
+    BSP_TRY(bsp_alloc(ctx, &d_r, (size_t)nnzb));
+    BSP_TRY(bsp_alloc(ctx, &d_c, (size_t)nnzb));
+    BSP_TRY(bsp_alloc(ctx, &d_v, (size_t)nnzb * kk));
+    if (nnzb) {
+        BSP_CUDA(ctx, cudaMemcpyAsync(d_r, brow, (size_t)nnzb * 4, cudaMemcpyHostToDevice, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(d_c, bcol, (size_t)nnzb * 4, cudaMemcpyHostToDevice, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(d_v, vals, (size_t)nnzb * kk * 8, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    int rc = bsp_ingest_coo(ctx, rows, cols, k, nnzb, d_r, d_c, d_v, max_row, max_col, out);
+    bsp_release(ctx, d_r); bsp_release(ctx, d_c); bsp_release(ctx, d_v);
+    if (rc == BSP_OK) BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // host buffers may be reused on return
+    return rc;
+}
+
+int bsp_mat_info(const bsp_mat *m, int32_t *rows, int32_t *cols, int32_t *k, int64_t *nnzb)
+{
+    if (!m) return BSP_ERR_ARG;
+    if (rows) *rows = m->rows;
+    if (cols) *cols = m->cols;
+    if (k) *k = m->k;
+    if (nnzb) *nnzb = m->nnzb;
+    return BSP_OK;
+}
+
+int bsp_mat_to_coo(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol, uint64_t *vals)
+{
+    if (!ctx || !valid_mat(m)) return BSP_ERR_ARG;
+    if (m->nnzb == 0) return BSP_OK;
+    BSP_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t kk = (size_t)m->k * m->k;
+    if (brow) {
+        int32_t *d_brow = nullptr;
+        BSP_TRY(bsp_alloc(ctx, &d_brow, (size_t)m->nnzb));
+        BSP_TRY(bsp_expand_rows(ctx, m, d_brow));
+        BSP_CUDA(ctx, cudaMemcpyAsync(brow, d_brow, (size_t)m->nnzb * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        bsp_release(ctx, d_brow);
+    }
+    if (bcol) BSP_CUDA(ctx, cudaMemcpyAsync(bcol, m->colidx, (size_t)m->nnzb * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (vals) BSP_CUDA(ctx, cudaMemcpyAsync(vals, m->vals, (size_t)m->nnzb * kk * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSP_OK;
+}
+
+int bsp_mat_device_view(const bsp_mat *m, int32_t *nbrows, int32_t *nbcols, const int32_t **d_rowptr,
+                        const int32_t **d_colidx, const uint64_t **d_vals)
+{
+    if (!valid_mat(m)) return BSP_ERR_ARG;
+    if (nbrows) *nbrows = m->nbr;
+    if (nbcols) *nbcols = m->nbc;
+    if (d_rowptr) *d_rowptr = m->rowptr;
+    if (d_colidx) *d_colidx = m->colidx;
+    if (d_vals) *d_vals = m->vals;
+    return BSP_OK;
+}
+
+int bsp_mat_from_device_bcsr(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows, int32_t nbcols,
+                             int64_t nnzb, const int32_t *d_rowptr, const int32_t *d_colidx, const uint64_t *d_vals,
+                             bsp_mat **out)
+{
+    if (!ctx || !out) return BSP_ERR_ARG;
+    *out = nullptr;
+    if (k < 1 || nbrows < 0 || nbcols < 0 || nnzb < 0 || !d_rowptr)
+        BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_from_device_bcsr: bad arguments");
+    BSP_CUDA(ctx, cudaSetDevice(ctx->device));
+    bsp_mat tmp;
+    tmp.rows = rows; tmp.cols = cols; tmp.k = k; tmp.nbr = nbrows; tmp.nbc = nbcols; tmp.nnzb = nnzb;
+    tmp.rowptr = const_cast<int32_t *>(d_rowptr);
+    tmp.colidx = const_cast<int32_t *>(d_colidx);
+    tmp.vals = const_cast<uint64_t *>(d_vals);
+    tmp.device = ctx->device;
+    return clone_mat(ctx, &tmp, out);
+}
+
+void bsp_mat_free(bsp_ctx *ctx, bsp_mat *m)
+{
+    if (!m) return;
+    if (ctx) {
+        cudaSetDevice(ctx->device);
+        bsp_release(ctx, m->rowptr); bsp_release(ctx, m->colidx); bsp_release(ctx, m->vals);
+    } else {
+        cudaFree(m->rowptr); cudaFree(m->colidx); cudaFree(m->vals);
+    }
+    delete m;
+}
+
+int bsp_spgemm(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, bsp_mat **C, bsp_stats *stats)
+{
+    return spgemm_impl(ctx, A, B, 0, INT32_MAX, C, stats);
+}
+
+int bsp_spgemm_panel(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo, int32_t row_hi, bsp_mat **C,
+                     bsp_stats *stats)
+{
+    if (ctx && row_lo > row_hi) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm_panel: row_lo > row_hi");
+    return spgemm_impl(ctx, A, B, row_lo, row_hi, C, stats);
+}
+
+int bsp_chain(bsp_ctx *ctx, bsp_mat *const *mats, int32_t n, bsp_mat **out, bsp_stats *stats, char *log,
+              size_t log_cap, int32_t log_base)
+{
+    if (!ctx || !out) return BSP_ERR_ARG;
+    *out = nullptr;
+    if (n < 1 || !mats) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_chain: empty chain");
+    for (int i = 0; i < n; i++)
+        if (!valid_mat(mats[i])) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_chain: matrix %d is null", i);
+    bsp_stats tot;
+    memset(&tot, 0, sizeof(tot));
+    size_t lp = 0;
+    if (log && log_cap) log[0] = 0;
+    // level 0 borrows the inputs; later levels own their matrices
+    std::vector<bsp_mat *> cur(mats, mats + n);
+    std::vector<char> owned((size_t)n, 0);
+    int rc = BSP_OK;
+    while (cur.size() > 1 && rc == BSP_OK) {
+        const size_t len = cur.size();
+        std::vector<bsp_mat *> nxt;
+        std::vector<char> nxt_owned;
+        for (size_t ind = 0; ind + 1 < len; ind += 2) { // cu:297: adjacent pairs
+            if (log && lp + 48 < log_cap)
+                lp += (size_t)snprintf(log + lp, log_cap - lp, "multiplying %d %d\n", log_base + (int)ind,
+                                       log_base + (int)ind + 1); // cu:301
+            bsp_mat *c = nullptr;
+            bsp_stats st;
+            rc = bsp_spgemm(ctx, cur[ind], cur[ind + 1], &c, &st);
+            if (rc != BSP_OK) { bsp_mat_free(ctx, c); break; }
+            accumulate(&tot, st);
+            nxt.push_back(c);
+            nxt_owned.push_back(1);
+            if (owned[ind]) { bsp_mat_free(ctx, cur[ind]); cur[ind] = nullptr; }
+            if (owned[ind + 1]) { bsp_mat_free(ctx, cur[ind + 1]); cur[ind + 1] = nullptr; }
+        }
+        if (rc == BSP_OK && (len & 1)) { // cu:318-320: odd tail carried unchanged
+            nxt.push_back(cur[len - 1]);
+            nxt_owned.push_back(owned[len - 1]);
+            cur[len - 1] = nullptr;
+        }
+        if (rc != BSP_OK) {
+            for (size_t i = 0; i < nxt.size(); i++) if (nxt_owned[i]) bsp_mat_free(ctx, nxt[i]);
+            for (size_t i = 0; i < cur.size(); i++) if (cur[i] && owned[i]) bsp_mat_free(ctx, cur[i]);
+            return rc;
+        }
+        cur.swap(nxt);
+        owned.swap(nxt_owned);
+    }
+    if (owned[0]) *out = cur[0];
+    else rc = clone_mat(ctx, cur[0], out); // n == 1: the reference leaves arr[start] as it is
+    if (stats) *stats = tot;
+    return rc;
+}
+
+int bsp_prune_zero(bsp_ctx *ctx, bsp_mat *m)
+{
+    if (!ctx || !valid_mat(m)) return BSP_ERR_ARG;
+    BSP_CUDA(ctx, cudaSetDevice(ctx->device));
+    return bsp_prune_device(ctx, m);
+}
+
+int bsp_multiply_host(bsp_ctx *ctx, int32_t k, int32_t rows_a, int32_t cols_a, int64_t nnzb_a, const int32_t *brow_a,
+                      const int32_t *bcol_a, const uint64_t *vals_a, int32_t rows_b, int32_t cols_b, int64_t nnzb_b,
+                      const int32_t *brow_b, const int32_t *bcol_b, const uint64_t *vals_b, int64_t cap_c,
+                      int64_t *nnzb_c, int32_t *brow_c, int32_t *bcol_c, uint64_t *vals_c, bsp_stats *stats)
+{
+    if (!ctx || !nnzb_c) return BSP_ERR_ARG;
+    bsp_mat *A = nullptr, *B = nullptr, *C = nullptr;
+    int rc = bsp_mat_from_coo(ctx, rows_a, cols_a, k, nnzb_a, brow_a, bcol_a, vals_a, &A);
+    if (rc == BSP_OK) rc = bsp_mat_from_coo(ctx, rows_b, cols_b, k, nnzb_b, brow_b, bcol_b, vals_b, &B);
+    if (rc == BSP_OK) rc = bsp_spgemm(ctx, A, B, &C, stats);
+    if (rc == BSP_OK) {
+        *nnzb_c = C->nnzb;
+        if (brow_c || bcol_c || vals_c) {
+            if (C->nnzb > cap_c) {
+                snprintf(ctx->err, sizeof(ctx->err), "bsp_multiply_host: result has %lld tiles, capacity %lld",
+                         (long long)C->nnzb, (long long)cap_c);
+                rc = BSP_ERR_LIMIT;
+            } else {
+                rc = bsp_mat_to_coo(ctx, C, brow_c, bcol_c, vals_c);
+            }
+        }
+    }
+    bsp_mat_free(ctx, A); bsp_mat_free(ctx, B); bsp_mat_free(ctx, C);
+    return rc;
+}
+
+} // extern "C"

@@ -1,0 +1,116 @@
+// bsp_internal.h -- shared declarations of libbspgemm (not part of the public ABI).
+//
+// Data layout in HBM: a matrix is CSR-of-blocks,
+//   rowptr [nbr+1] int32   block-row r owns tiles rowptr[r] .. rowptr[r+1]-1
+//   colidx [nnzb]  int32   block-column of each tile, ascending inside a row
+//   vals   [nnzb*k*k] u64  tiles back to back, each row-major (512 B for k=8, 128 B for k=4)
+// which is the reference's ordered std::map<(brow,bcol), tile> (cu:26-32) flattened in
+// iteration order.  nbr = 1 + largest block-row coordinate seen (block coordinates are
+// opaque ints in the reference, cu:150-151; they are never scaled by k).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/bspgemm.h"
+
+struct bsp_ctx {
+    int device;
+    cudaStream_t stream;
+    bool owns_stream;
+    int sm_count;
+    int64_t launches;
+    cudaEvent_t ev[4];
+    void *pinned;        // small pinned staging area for scalar read-backs
+    size_t pinned_bytes;
+    char err[512];
+};
+
+struct bsp_mat {
+    int32_t rows, cols, k;
+    int32_t nbr, nbc;    // block-row / block-column index space (max coordinate + 1)
+    int64_t nnzb;
+    int32_t *rowptr;     // device
+    int32_t *colidx;     // device
+    uint64_t *vals;      // device
+    int device;
+};
+
+#define BSP_FAIL(ctx, code, ...)                                  \
+    do {                                                          \
+        snprintf((ctx)->err, sizeof((ctx)->err), __VA_ARGS__);    \
+        return (code);                                            \
+    } while (0)
+
+#define BSP_CUDA(ctx, call)                                                                  \
+    do {                                                                                     \
+        cudaError_t e_ = (call);                                                             \
+        if (e_ != cudaSuccess) {                                                             \
+            snprintf((ctx)->err, sizeof((ctx)->err), "%s:%d: %s failed: %s", __FILE__,       \
+                     __LINE__, #call, cudaGetErrorString(e_));                               \
+            return (e_ == cudaErrorMemoryAllocation) ? BSP_ERR_NOMEM : BSP_ERR_CUDA;         \
+        }                                                                                    \
+    } while (0)
+
+#define BSP_TRY(expr)                  \
+    do {                               \
+        int rc_ = (expr);              \
+        if (rc_ != BSP_OK) return rc_; \
+    } while (0)
+
+// stream-ordered allocation on the context's stream
+template <typename T>
+static inline int bsp_alloc(bsp_ctx *ctx, T **p, size_t count)
+{
+    *p = nullptr;
+    size_t bytes = (count ? count : 1) * sizeof(T);
+    cudaError_t e = cudaMallocAsync((void **)p, bytes, ctx->stream);
+    if (e != cudaSuccess) {
+        snprintf(ctx->err, sizeof(ctx->err), "device allocation of %zu bytes failed: %s", bytes,
+                 cudaGetErrorString(e));
+        cudaGetLastError();
+        return BSP_ERR_NOMEM;
+    }
+    return BSP_OK;
+}
+static inline void bsp_release(bsp_ctx *ctx, void *p)
+{
+    if (p) cudaFreeAsync(p, ctx->stream);
+}
+
+#define BSP_LAUNCH_CHECK(ctx)                  \
+    do {                                       \
+        (ctx)->launches++;                     \
+        BSP_CUDA(ctx, cudaGetLastError());     \
+    } while (0)
+
+// ---- phases (each defined in its own .cu) ---------------------------------------------------
+
+// exclusive scans on the context's stream; out may alias in; out[n] is NOT written (n values in, n out)
+int bsp_scan_i32(bsp_ctx *ctx, const int32_t *in, int32_t *out, int64_t n, int32_t *total_dev);
+int bsp_scan_i32_to_i64(bsp_ctx *ctx, const int32_t *in, int64_t *out, int64_t n);
+
+struct bsp_symbolic_out {
+    int32_t *c_rowptr;   // [nbr+1]
+    int32_t *c_colidx;   // [nnzb_c]
+    int64_t *pair_ptr;   // [nnzb_c+1]
+    int2 *pairs;         // [nprod]  (index of A tile, index of B tile), ascending inner block index
+    int64_t nnzb_c;
+    int64_t nprod;
+};
+
+// GPU symbolic pass (replaces the host hash maps of cu:141-176 and the pack loop cu:189-218)
+int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo, int32_t row_hi,
+                 bsp_symbolic_out *out);
+
+// numeric pass (replaces matrix_multiplyKernel cu:44-66 and the 500-key rounds cu:181-270)
+int bsp_numeric(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym,
+                uint64_t *c_vals, int64_t *exact_refolds, int32_t *path);
+
+int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m);
+int bsp_expand_rows(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_brow);
+int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,
+                   const int32_t *d_brow, const int32_t *d_bcol, const uint64_t *d_vals,
+                   int32_t max_row, int32_t max_col, bsp_mat **out);

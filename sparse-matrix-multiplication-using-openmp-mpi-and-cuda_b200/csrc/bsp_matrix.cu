@@ -1,0 +1,227 @@
+// bsp_matrix.cu -- building, exporting and compacting CSR-of-blocks matrices on device.
+//
+//   ingest : coordinate list (file order, maybe unsorted, maybe duplicate keys) -> CSR of
+//            blocks.  Stands in for the reader's map insert m[{row,col}] = v (cu:383) and
+//            the flatten step of helper (cu:102-138).  The key sort uses CUB's radix sort
+//            (library plumbing on the ingest side, not on the multiply path).
+//   expand : rowptr -> one block-row coordinate per tile, for the sorted coordinate export
+//            that the writer needs (cu:598-599).
+//   prune  : drop all-zero tiles of the final product (intended semantics of cu:577-592):
+//            per-tile predicate, exclusive scan, compaction of colidx / vals / rowptr.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "bsp_internal.h"
+
+namespace {
+
+__global__ void make_keys_kernel(const int32_t *__restrict__ brow, const int32_t *__restrict__ bcol, int64_t n,
+                                 uint64_t *__restrict__ keys, int32_t *__restrict__ idx)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        keys[i] = ((uint64_t)(uint32_t)brow[i] << 32) | (uint32_t)bcol[i];
+        idx[i] = (int32_t)i;
+    }
+}
+
+// keep the LAST entry of each run of equal keys (cu:383: later insert overwrites)
+__global__ void flag_last_kernel(const uint64_t *__restrict__ keys, int64_t n, int32_t *__restrict__ keep)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keep[i] = (i + 1 == n || keys[i + 1] != keys[i]) ? 1 : 0;
+    if (i == n) keep[i] = 0;
+}
+
+// one thread per sorted entry: write colidx and the rowptr boundaries it is responsible for
+__global__ void scatter_index_kernel(const uint64_t *__restrict__ keys, const int32_t *__restrict__ keep,
+                                     const int32_t *__restrict__ pos, int64_t n, int32_t nbr,
+                                     int32_t *__restrict__ rowptr, int32_t *__restrict__ colidx)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !keep[i]) return;
+    const int32_t o = pos[i];
+    const int32_t row = (int32_t)(keys[i] >> 32);
+    colidx[o] = (int32_t)(keys[i] & 0xffffffffu);
+    // previous kept entry's row (kept entries have distinct keys; find the previous distinct key)
+    int32_t prev_row = -1;
+    int64_t j = i - 1;
+    while (j >= 0 && keys[j] == keys[i]) j--; // cannot happen for a kept (last) entry's successors, only predecessors
+    if (j >= 0) prev_row = (int32_t)(keys[j] >> 32);
+    for (int32_t r = prev_row + 1; r <= row; r++) rowptr[r] = o;
+    if (o == pos[n] - 1)
+        for (int32_t r = row + 1; r <= nbr; r++) rowptr[r] = o + 1;
+}
+
+// gather tiles: one CTA-strided loop over (tile, 16-byte chunk)
+__global__ void gather_tiles_kernel(const uint64_t *__restrict__ src, const int32_t *__restrict__ idx,
+                                    const int32_t *__restrict__ keep, const int32_t *__restrict__ pos, int64_t n,
+                                    int kk, uint64_t *__restrict__ dst)
+{
+    const int64_t total = n * kk;
+    for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = g / kk;
+        const int e = (int)(g - i * kk);
+        if (keep[i]) dst[(size_t)pos[i] * kk + e] = src[(size_t)idx[i] * kk + e];
+    }
+}
+
+__global__ void expand_rows_kernel(const int32_t *__restrict__ rowptr, int32_t nbr, int64_t nnzb,
+                                   int32_t *__restrict__ brow)
+{
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nnzb) return;
+    int lo = 0, hi = nbr; // largest r with rowptr[r] <= t
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (rowptr[mid] <= t) lo = mid; else hi = mid;
+    }
+    brow[t] = lo;
+}
+
+// one warp per tile: keep = any entry non-zero (cu:580-586)
+__global__ void tile_nonzero_kernel(const uint64_t *__restrict__ vals, int64_t nnzb, int kk, int32_t *__restrict__ keep)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t t = warp; t < nnzb; t += nwarps) {
+        const uint64_t *v = vals + (size_t)t * kk;
+        uint64_t acc = 0;
+        for (int e = lane; e < kk; e += 32) acc |= v[e];
+        const unsigned any = __ballot_sync(0xffffffffu, acc != 0);
+        if (lane == 0) keep[t] = any ? 1 : 0;
+    }
+    if (warp == 0 && lane == 0) keep[nnzb] = 0;
+}
+
+__global__ void compact_tiles_kernel(const uint64_t *__restrict__ vals, const int32_t *__restrict__ colidx,
+                                     const int32_t *__restrict__ keep, const int32_t *__restrict__ pos, int64_t nnzb,
+                                     int kk, uint64_t *__restrict__ vals_out, int32_t *__restrict__ colidx_out)
+{
+    const int64_t total = nnzb * kk;
+    for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t t = g / kk;
+        const int e = (int)(g - t * kk);
+        if (keep[t]) {
+            vals_out[(size_t)pos[t] * kk + e] = vals[g];
+            if (e == 0) colidx_out[pos[t]] = colidx[t];
+        }
+    }
+}
+
+__global__ void remap_rowptr_kernel(const int32_t *__restrict__ rowptr, int32_t nbr, const int32_t *__restrict__ pos,
+                                    int32_t *__restrict__ rowptr_out)
+{
+    int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r <= nbr) rowptr_out[r] = pos[rowptr[r]];
+}
+
+inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads > 0 ? (n + threads - 1) / threads : 1); }
+
+} // namespace
+
+int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb, const int32_t *d_brow,
+                   const int32_t *d_bcol, const uint64_t *d_vals, int32_t max_row, int32_t max_col, bsp_mat **out)
+{
+    bsp_mat *m = new bsp_mat();
+    m->rows = rows; m->cols = cols; m->k = k; m->device = ctx->device;
+    m->nbr = nnzb > 0 ? max_row + 1 : 0;
+    m->nbc = nnzb > 0 ? max_col + 1 : 0;
+    m->nnzb = 0; m->rowptr = nullptr; m->colidx = nullptr; m->vals = nullptr;
+    *out = m;
+    const int kk = k * k;
+    BSP_TRY(bsp_alloc(ctx, &m->rowptr, (size_t)m->nbr + 1));
+    if (nnzb == 0) {
+        BSP_CUDA(ctx, cudaMemsetAsync(m->rowptr, 0, sizeof(int32_t), ctx->stream));
+        BSP_TRY(bsp_alloc(ctx, &m->colidx, 1));
+        BSP_TRY(bsp_alloc(ctx, &m->vals, 1));
+        return BSP_OK;
+    }
+    uint64_t *keys = nullptr, *keys2 = nullptr;
+    int32_t *idx = nullptr, *idx2 = nullptr, *keep = nullptr, *pos = nullptr;
+    BSP_TRY(bsp_alloc(ctx, &keys, (size_t)nnzb));
+    BSP_TRY(bsp_alloc(ctx, &keys2, (size_t)nnzb));
+    BSP_TRY(bsp_alloc(ctx, &idx, (size_t)nnzb));
+    BSP_TRY(bsp_alloc(ctx, &idx2, (size_t)nnzb));
+    BSP_TRY(bsp_alloc(ctx, &keep, (size_t)nnzb + 1));
+    BSP_TRY(bsp_alloc(ctx, &pos, (size_t)nnzb + 1));
+    make_keys_kernel<<<blocks_for(nnzb, 256), 256, 0, ctx->stream>>>(d_brow, d_bcol, nnzb, keys, idx);
+    BSP_LAUNCH_CHECK(ctx);
+    size_t tmp_bytes = 0;
+    BSP_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, idx, idx2, (int)nnzb, 0, 64, ctx->stream));
+    char *tmp = nullptr;
+    BSP_TRY(bsp_alloc(ctx, &tmp, tmp_bytes));
+    BSP_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, idx, idx2, (int)nnzb, 0, 64, ctx->stream));
+    ctx->launches += 1;
+    flag_last_kernel<<<blocks_for(nnzb + 1, 256), 256, 0, ctx->stream>>>(keys2, nnzb, keep);
+    BSP_LAUNCH_CHECK(ctx);
+    BSP_TRY(bsp_scan_i32(ctx, keep, pos, nnzb + 1, nullptr));
+    int32_t *h_uniq = (int32_t *)ctx->pinned;
+    BSP_CUDA(ctx, cudaMemcpyAsync(h_uniq, pos + nnzb, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    m->nnzb = *h_uniq;
+    BSP_TRY(bsp_alloc(ctx, &m->colidx, (size_t)m->nnzb));
+    BSP_TRY(bsp_alloc(ctx, &m->vals, (size_t)m->nnzb * kk));
+    scatter_index_kernel<<<blocks_for(nnzb, 256), 256, 0, ctx->stream>>>(keys2, keep, pos, nnzb, m->nbr, m->rowptr,
+                                                                         m->colidx);
+    BSP_LAUNCH_CHECK(ctx);
+    {
+        int64_t total = nnzb * kk;
+        int64_t g = (total + 255) / 256;
+        if (g > (int64_t)ctx->sm_count * 32) g = (int64_t)ctx->sm_count * 32;
+        gather_tiles_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>(d_vals, idx2, keep, pos, nnzb, kk, m->vals);
+        BSP_LAUNCH_CHECK(ctx);
+    }
+    bsp_release(ctx, keys); bsp_release(ctx, keys2); bsp_release(ctx, idx); bsp_release(ctx, idx2);
+    bsp_release(ctx, keep); bsp_release(ctx, pos); bsp_release(ctx, tmp);
+    return BSP_OK;
+}
+
+int bsp_expand_rows(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_brow)
+{
+    if (m->nnzb == 0) return BSP_OK;
+    expand_rows_kernel<<<blocks_for(m->nnzb, 256), 256, 0, ctx->stream>>>(m->rowptr, m->nbr, m->nnzb, d_brow);
+    BSP_LAUNCH_CHECK(ctx);
+    return BSP_OK;
+}
+
+int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m)
+{
+    if (m->nnzb == 0) return BSP_OK;
+    const int kk = m->k * m->k;
+    int32_t *keep = nullptr, *pos = nullptr;
+    BSP_TRY(bsp_alloc(ctx, &keep, (size_t)m->nnzb + 1));
+    BSP_TRY(bsp_alloc(ctx, &pos, (size_t)m->nnzb + 1));
+    {
+        int64_t g = (m->nnzb * 32 + 255) / 256;
+        if (g > (int64_t)ctx->sm_count * 16) g = (int64_t)ctx->sm_count * 16;
+        tile_nonzero_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>(m->vals, m->nnzb, kk, keep);
+        BSP_LAUNCH_CHECK(ctx);
+    }
+    BSP_TRY(bsp_scan_i32(ctx, keep, pos, m->nnzb + 1, nullptr));
+    int32_t *h_kept = (int32_t *)ctx->pinned;
+    BSP_CUDA(ctx, cudaMemcpyAsync(h_kept, pos + m->nnzb, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int64_t kept = *h_kept;
+    if (kept != m->nnzb) {
+        int32_t *rowptr2 = nullptr, *colidx2 = nullptr;
+        uint64_t *vals2 = nullptr;
+        BSP_TRY(bsp_alloc(ctx, &rowptr2, (size_t)m->nbr + 1));
+        BSP_TRY(bsp_alloc(ctx, &colidx2, (size_t)kept));
+        BSP_TRY(bsp_alloc(ctx, &vals2, (size_t)kept * kk));
+        int64_t total = m->nnzb * kk;
+        int64_t g = (total + 255) / 256;
+        if (g > (int64_t)ctx->sm_count * 32) g = (int64_t)ctx->sm_count * 32;
+        compact_tiles_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>(m->vals, m->colidx, keep, pos, m->nnzb, kk, vals2,
+                                                                    colidx2);
+        BSP_LAUNCH_CHECK(ctx);
+        remap_rowptr_kernel<<<blocks_for((int64_t)m->nbr + 1, 256), 256, 0, ctx->stream>>>(m->rowptr, m->nbr, pos,
+                                                                                            rowptr2);
+        BSP_LAUNCH_CHECK(ctx);
+        bsp_release(ctx, m->rowptr); bsp_release(ctx, m->colidx); bsp_release(ctx, m->vals);
+        m->rowptr = rowptr2; m->colidx = colidx2; m->vals = vals2; m->nnzb = kept;
+    }
+    bsp_release(ctx, keep);
+    bsp_release(ctx, pos);
+    return BSP_OK;
+}

@@ -1,0 +1,265 @@
+"""Parity of the CUDA path (called through the C ABI) against the CPU oracle and the golden
+fixtures made by the reference's own code.  Integer work: the bar is bit-exact."""
+import hashlib
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+import bsp_dist
+import bsp_gen
+import bspgemm
+import orc
+import util
+
+pytestmark = pytest.mark.gpu
+KATS = util.load_kats()
+MAXV = (1 << 64) - 1
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = bspgemm.Context(0)
+    yield c
+    c.close()
+
+
+def dev(ctx, m):
+    return ctx.matrix_from_coo(*m)
+
+
+def assert_same(gpu_mat, oracle_mat):
+    br, bc, v = gpu_mat.to_coo()
+    rbr, rbc, rv = oracle_mat.coo()
+    assert gpu_mat.nnzb == oracle_mat.nnzb
+    assert np.array_equal(br, rbr) and np.array_equal(bc, rbc)
+    assert np.array_equal(v, rv)
+    assert (gpu_mat.rows, gpu_mat.cols) == (oracle_mat.rows, oracle_mat.cols)
+
+
+@pytest.mark.parametrize("case", KATS, ids=[c["id"] for c in KATS])
+def test_golden_cases(ctx, case):
+    """Known answers from the reference program, incl. its P-rank association trees."""
+    k = case["k"]
+    mats = [ctx.matrix_from_coo(r, c, k, br, bc, v) for r, c, br, bc, v in util.case_mats(case)]
+    res = bsp_dist.chain_ranks_on_one_context(ctx, mats, case["ranks"])
+    if res in mats:  # single matrix: helper2 returns a copy
+        res = ctx.helper2([res])
+    res.prune_zero()
+    br, bc, v = res.to_coo()
+    assert util.matrix_text(res.rows, res.cols, k, br, bc, v) == case["matrix_text"]
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "matrix")
+        res.write_text(p)
+        assert open(p).read() == case["matrix_text"]
+
+
+@pytest.mark.parametrize("case", [c for c in KATS if c["multiplying"] is not None], ids=lambda c: c["id"])
+def test_golden_tree_log(ctx, case):
+    k = case["k"]
+    mats = [ctx.matrix_from_coo(r, c, k, br, bc, v) for r, c, br, bc, v in util.case_mats(case)]
+    _, log = ctx.helper2(mats, want_log=True)
+    assert [list(map(int, ln.split()[1:])) for ln in log.splitlines()] == case["multiplying"]
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 5, 7, 8, 12, 16, 32])
+@pytest.mark.parametrize("kind", ["edgy", "u64"])
+def test_pair_vs_oracle_all_tile_sizes(ctx, k, kind):
+    G = 24 if k <= 8 else 8
+    a = bsp_gen.random_matrix(G * k, (G + 5) * k, k, 0.2, 40 + k, kind)
+    b = bsp_gen.random_matrix((G + 5) * k, (G - 3) * k, k, 0.25, 90 + k, kind)
+    st = bspgemm.Stats()
+    c = ctx.helper(dev(ctx, a), dev(ctx, b), stats=st)
+    ref, nprod = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))
+    assert st.nprod == nprod and st.nnzb_c == ref.nnzb
+    assert_same(c, ref)
+
+
+@pytest.mark.parametrize("k,G,n,dens", [(4, 40, 6, 0.06), (8, 24, 5, 0.1), (2, 30, 9, 0.1), (4, 64, 16, 0.03)])
+def test_chain_vs_oracle(ctx, k, G, n, dens):
+    host = [bsp_gen.random_matrix(G * k, G * k, k, dens, 500 + 13 * i, "edgy" if i % 2 else "u64") for i in range(n)]
+    res = ctx.helper2([dev(ctx, m) for m in host]).prune_zero()
+    ref = orc.chain([orc.OMat.from_coo(*m) for m in host])[0].prune_zero()
+    assert_same(res, ref)
+
+
+@pytest.mark.parametrize("P", [2, 3, 4, 8])
+def test_rank_trees_vs_oracle(ctx, P):
+    k, G, n = 2, 10, 11
+    host = [bsp_gen.random_matrix(G * k, G * k, k, 0.35, 700 + i, "edgy") for i in range(n)]
+    res = bsp_dist.chain_ranks_on_one_context(ctx, [dev(ctx, m) for m in host], P).prune_zero()
+    ref = orc.chain([orc.OMat.from_coo(*m) for m in host], ranks=P)[0].prune_zero()
+    assert_same(res, ref)
+
+
+@pytest.mark.parametrize("cfg", util.load_cfg1(), ids=lambda c: c["id"])
+def test_cfg1_output_file_hash(ctx, cfg):
+    """BASELINE.json configs[0]: n=1024, k=4, 5 % -- byte-identical output file."""
+    mats = [dev(ctx, bsp_gen.random_matrix(cfg["n"], cfg["n"], cfg["k"], cfg["density"], s, cfg["kind"]))
+            for s in cfg["seeds"]]
+    res = ctx.helper2(mats).prune_zero()
+    assert res.nnzb == cfg["out_nnzb"]
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "matrix")
+        res.write_text(p)
+        assert hashlib.sha256(open(p, "rb").read()).hexdigest() == cfg["sha256"]
+
+
+def test_edge_cases(ctx):
+    k = 4
+    a = bsp_gen.random_matrix(64, 64, k, 0.3, 1, "u64")
+    empty = (64, 64, k, np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.uint64))
+    A, E = dev(ctx, a), dev(ctx, empty)
+    for x, y in ((A, E), (E, A), (E, E)):
+        c = ctx.helper(x, y)
+        assert c.nnzb == 0 and c.to_coo()[0].size == 0
+        assert c.prune_zero().nnzb == 0
+    # inner indices that never match, and A columns beyond B's last block row
+    a2 = (64, 64, k, np.array([0, 1], np.int32), np.array([50, 60], np.int32), np.ones(2 * 16, np.uint64))
+    b2 = (64, 64, k, np.array([2, 3], np.int32), np.array([0, 1], np.int32), np.ones(2 * 16, np.uint64))
+    assert ctx.helper(dev(ctx, a2), dev(ctx, b2)).nnzb == 0
+    # ragged: one very long row, many empty rows, max values
+    br = np.zeros(300, np.int32)
+    bc = np.arange(300, dtype=np.int32) * 3
+    v = np.full(300 * 16, MAXV, np.uint64)
+    long_a = (1200, 1200, k, br, bc, v)
+    b3 = bsp_gen.random_matrix(1200 * 3, 1200, k, 0.05, 5, "edgy")
+    c = ctx.helper(dev(ctx, long_a), dev(ctx, b3))
+    assert_same(c, orc.multiply(orc.OMat.from_coo(*long_a), orc.OMat.from_coo(*b3))[0])
+    # negative coordinates are rejected with a message, not a crash
+    with pytest.raises(bspgemm.BspError) as e:
+        ctx.matrix_from_coo(8, 8, k, [-1], [0], np.ones(16, np.uint64))
+    assert e.value.code == 1
+    # tile-edge mismatch
+    with pytest.raises(bspgemm.BspError):
+        ctx.helper(A, dev(ctx, bsp_gen.random_matrix(64, 64, 8, 0.3, 1, "u64")))
+
+
+def test_duplicates_and_unsorted_ingest(ctx):
+    k = 2
+    br = np.array([3, 0, 3, 1, 0, 3], np.int32)
+    bc = np.array([1, 2, 1, 1, 2, 0], np.int32)
+    v = np.arange(6 * 4, dtype=np.uint64)
+    m = ctx.matrix_from_coo(8, 8, k, br, bc, v)
+    o = orc.OMat.from_coo(8, 8, k, br, bc, v)
+    assert_same(m, o)
+    assert m.nnzb == 4
+
+
+def test_panels_concatenate_to_full_product(ctx):
+    k, G = 8, 96
+    a = bsp_gen.random_matrix(G * k, G * k, k, 0.08, 21, "u64")
+    b = bsp_gen.random_matrix(G * k, G * k, k, 0.08, 22, "u64")
+    A, B = dev(ctx, a), dev(ctx, b)
+    full = ctx.helper(A, B).to_coo()
+    bounds = [0, 7, 40, 41, G]
+    parts = [ctx.helper(A, B, panel=(bounds[i], bounds[i + 1])).to_coo() for i in range(4)]
+    for j in range(3):
+        assert np.array_equal(np.concatenate([p[j] for p in parts]), full[j])
+
+
+def test_multiply_host_single_call(ctx):
+    k = 4
+    a = bsp_gen.random_matrix(256, 256, k, 0.1, 31, "edgy")
+    b = bsp_gen.random_matrix(256, 256, k, 0.1, 32, "edgy")
+    st = bspgemm.Stats()
+    br, bc, v = ctx.multiply_host(k, (a[0], a[1], a[3], a[4], a[5]), (b[0], b[1], b[3], b[4], b[5]), stats=st)
+    ref = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))[0]
+    rbr, rbc, rv = ref.coo()
+    assert np.array_equal(br, rbr) and np.array_equal(bc, rbc) and np.array_equal(v, rv)
+    assert st.launches > 0
+
+
+def test_a4_cli_matches_reference_files(ctx):
+    exe = os.path.join(os.path.dirname(bspgemm.__file__), "a4")
+    import make_golden_inputs
+    for case in KATS:
+        with tempfile.TemporaryDirectory() as d:
+            make_golden_inputs.write_raw_folder(os.path.join(d, "in"), util.case_mats(case), case["k"])
+            p = subprocess.run([exe, os.path.join(d, "in"), "--ranks", str(case["ranks"]), "--devices", "1"], cwd=d,
+                               stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=120)
+            assert p.returncode == 0, p.stderr.decode()
+            assert open(os.path.join(d, "matrix")).read() == case["matrix_text"], case["id"]
+            out = p.stdout.decode()
+            assert "time taken" in out
+            if case["multiplying"] is not None:
+                got = [list(map(int, ln.split()[1:])) for ln in out.splitlines() if ln.startswith("multiplying")]
+                assert got == case["multiplying"]
+    with tempfile.TemporaryDirectory() as d:
+        p = subprocess.run([exe, os.path.join(d, "missing")], cwd=d, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert p.returncode == 1 and b"Cannot open size file!" in p.stderr
+
+
+# ---- size-independent properties at BASELINE.json's full sizes -------------------------------
+
+def block_identity(G, k):
+    br = np.arange(G, dtype=np.int32)
+    v = np.tile(np.eye(k, dtype=np.uint64).reshape(-1), G)
+    return G * k, G * k, k, br, br.copy(), v
+
+
+def test_full_size_identity_and_sampled_tiles(ctx):
+    """configs[1] shape: n=65536, k=8, 1 % density. A*I == A == I*A bit for bit (entries are in
+    [1, 2^64-2], so the 2^64-1 edge never fires), and randomly sampled tiles of A*B equal a
+    numpy evaluation of the reference arithmetic."""
+    n, k, d = 65536, 8, 0.01
+    G = n // k
+    a = bsp_gen.random_matrix(n, n, k, d, 1234, "u64")
+    A = dev(ctx, a)
+    I = dev(ctx, block_identity(G, k))
+    for prod in (ctx.helper(A, I), ctx.helper(I, A)):
+        br, bc, v = prod.to_coo()
+        assert np.array_equal(br, a[3]) and np.array_equal(bc, a[4]) and np.array_equal(v, a[5])
+    b = bsp_gen.random_matrix(n, n, k, d, 1235, "u64")
+    st = bspgemm.Stats()
+    Cm = ctx.helper(A, dev(ctx, b), stats=st)
+    br, bc, v = Cm.to_coo()
+    # pattern: sortedness + counts
+    key = br.astype(np.int64) * G + bc
+    assert np.all(np.diff(key) > 0)
+    rowlen_b = np.bincount(b[3], minlength=G)
+    assert st.nprod == int(rowlen_b[a[4]].sum())
+    # sampled tiles, evaluated with python ints in reference order
+    rng = np.random.default_rng(7)
+    a_key = a[3].astype(np.int64) * G + a[4]
+    b_key = b[3].astype(np.int64) * G + b[4]
+    for t in rng.integers(0, br.size, 40):
+        i, c = int(br[t]), int(bc[t])
+        js = a[4][np.searchsorted(a[3], i):np.searchsorted(a[3], i + 1)]
+        acc = [[0] * k for _ in range(k)]
+        hit = 0
+        for j in js:
+            q = np.searchsorted(b_key, int(j) * G + c)
+            if q < b_key.size and b_key[q] == int(j) * G + c:
+                hit += 1
+                At = a[5][np.searchsorted(a_key, i * G + int(j))]
+                Bt = b[5][q]
+                for r in range(k):
+                    for cc in range(k):
+                        s = acc[r][cc]
+                        for x in range(k):
+                            p = (int(At[r, x]) * int(Bt[x, cc])) & MAXV
+                            p = 0 if p == MAXV else p
+                            s = (s + p) & MAXV
+                            s = 0 if s == MAXV else s
+                        acc[r][cc] = s
+        assert hit >= 1
+        assert np.array_equal(np.array(acc, dtype=np.uint64), v[t])
+
+
+def test_full_size_chain_is_associative_without_edge_hits(ctx):
+    """n=16384, k=4 (configs[2] shape), short chain: with entries that never produce 2^64-1 the
+    arithmetic is the ring Z/2^64, so every association tree gives the same bits."""
+    n, k = 16384, 4
+    G = n // k
+    mats = [dev(ctx, bsp_gen.random_matrix(n, n, k, 2.0 / G, 4000 + i, "u64")) for i in range(8)]
+    r1 = ctx.helper2(mats).to_coo()
+    r2 = bsp_dist.chain_ranks_on_one_context(ctx, mats, 4).to_coo()
+    left = mats[0]
+    for m in mats[1:]:
+        left = ctx.helper(left, m)
+    r3 = left.to_coo()
+    for x, y, z in zip(r1, r2, r3):
+        assert np.array_equal(x, y) and np.array_equal(x, z)
