@@ -1,0 +1,348 @@
+#!/usr/bin/env python
+"""bench.py -- headline measurement of the block-sparse product path (BASELINE.json metric:
+SpGEMM useful GFLOP/s; chain milliseconds as a secondary figure).
+
+    python bench.py --gpus N --steps K --warmup W            our CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  the reference's own CPU path
+
+A step is one pass of the hot path (symbolic + numeric) over one synthetic workload:
+BASELINE.json configs[1], a single A*B with n=65536, k=8, 1 % block density, uint64 entries.
+At N > 1 every rank multiplies its own block-row panel A_r (seed differs per rank) by the
+same B -- the row-panel sharding of a taller A, which needs no data-path collective --
+so per-GPU work is fixed ("weak") and value = products of all ranks / max-over-ranks time.
+Useful ops = 2*k^3*nprod (one multiply + one add per inner step), SURVEY.md section 8d.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "sparse-matrix-multiplication-using-openmp-mpi-and-cuda_b200")
+sys.path.insert(0, PKG)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (n, k, density, value kind)
+    "cfg2": (65536, 8, 0.01, "u64"),
+    "cfg1": (1024, 4, 0.05, "u64"),
+    "mid": (16384, 8, 0.01, "u64"),
+}
+METRIC = "spgemm_useful_gflops"
+UNIT = "GFLOP/s"
+
+
+def workload_name(n, k, d):
+    return "single A*B, n=%d, k=%d, %.3g%% block density, uint64 entries (BASELINE.json configs[1] shape)" % (n, k, d * 100)
+
+
+def algorithmic_bytes(nnzb_a, nnzb_b, nnzb_c, G, k):
+    """Compulsory CSR-of-blocks traffic of the numeric pass."""
+    per = lambda nnzb: nnzb * k * k * 8 + 4 * nnzb + 4 * (G + 1)  # noqa: E731
+    return per(nnzb_a) + per(nnzb_b) + per(nnzb_c)
+
+
+def symbolic_bytes(nnzb_a, nprod, nnzb_c, G):
+    """SURVEY.md section 8d symbolic figure plus the pair lists this design writes."""
+    return 4 * nnzb_a + 4 * nprod + 4 * nnzb_c + 12 * (G + 1) + 8 * nprod + 8 * (nnzb_c + 1)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.rows.append([x.strip() for x in ln.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); smax.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, val in zip(names, r[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------------------
+# the reference arm / cpu_baseline: the reference's own translation unit built host-only
+# --------------------------------------------------------------------------------------------
+
+def reference_sample(n, k, d, seed_a, seed_b, rows_frac=8, inner_frac=8):
+    """A bounded sample of the workload for the CPU arm: block rows [0, G/rows_frac) of A and
+    inner block indices [0, G/inner_frac) (columns of A / rows of B), all columns of B."""
+    import bsp_gen
+    G = n // k
+    R, J = max(1, G // rows_frac), max(1, G // inner_frac)
+    _, _, _, abr, abc, av = bsp_gen.random_matrix(n, n, k, d, seed_a, "u64")
+    _, _, _, bbr, bbc, bv = bsp_gen.random_matrix(n, n, k, d, seed_b, "u64")
+    ka = (abr < R) & (abc < J)
+    kb = bbr < J
+    a = (R * k, J * k, k, abr[ka], abc[ka], av[ka])
+    b = (J * k, n, k, bbr[kb], bbc[kb], bv[kb])
+    nprod = int(np.bincount(b[3], minlength=J)[a[4]].sum())
+    desc = ("block rows [0,%d) of A x inner block indices [0,%d) x all %d block columns of B: %d x %d tiles, %d tile products"
+            % (R, J, G, a[3].size, b[3].size, nprod))
+    return a, b, nprod, desc
+
+
+def run_reference_once(folder, variant, threads):
+    """One timed run of the reference program; returns hot-path seconds (sum of its own phase
+    timers inside helper, cu:162-273) and its end-to-end 'time taken' (cu:679)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import orc
+    r = orc.run_ref(folder, ranks=1, variant=variant, threads=threads, keep_output=False)
+    if r["returncode"] != 0:
+        raise RuntimeError("reference run failed: " + r["stderr"][-500:])
+    hot = sum(r["phases"].values())
+    return hot, (r["time_taken"][0] if r["time_taken"] else None), r["phases"]
+
+
+def cpu_reference_measure(n, k, d, steps, warmup, use_all_threads=True):
+    """Times the reference's CPU path on a bounded sample. Returns dict for the JSON line."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import orc
+    cores = os.cpu_count() or 1
+    a, b, nprod, desc = reference_sample(n, k, d, 1000, 1001)
+    flop = 2.0 * k ** 3 * nprod
+    if orc.have_ref("ref_host_timed_omp"):
+        variant = "ref_host_timed_omp" if use_all_threads else "ref_host_timed"
+        threads = cores if use_all_threads else 1
+        with tempfile.TemporaryDirectory(prefix="bsp_cpu_") as folder:
+            orc.write_folder(folder, [orc.OMat.from_coo(*a), orc.OMat.from_coo(*b)], k)
+            times, e2e = [], []
+            for i in range(warmup + steps):
+                hot, tt, _ = run_reference_once(folder, variant, threads)
+                if i >= warmup:
+                    times.append(hot); e2e.append(tt)
+        sec = sum(times) / len(times)
+        return dict(value=flop / sec / 1e9, unit=UNIT, cores=threads, kind="reference",
+                    sample=desc + "; hot path = sum of the reference's own phase timers inside helper; "
+                    "kernel loop emulated on %d OpenMP threads, the rest single-threaded as shipped" % threads,
+                    seconds_hot_path=sec, seconds_end_to_end=(sum(e2e) / len(e2e)) if e2e and e2e[0] else None,
+                    nprod=nprod)
+    # the reference host build did not travel: time the C restatement instead
+    A, B = orc.OMat.from_coo(*a), orc.OMat.from_coo(*b)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        orc.multiply(A, B, threads=cores)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    sec = sum(times) / len(times)
+    return dict(value=flop / sec / 1e9, unit=UNIT, cores=cores, kind="port", sample=desc, seconds_hot_path=sec, nprod=nprod)
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n, k, d, _ = WORKLOADS[args.workload]
+    steps = max(1, min(args.steps, 5))
+    warm = min(args.warmup, 1)
+    cb = cpu_reference_measure(n, k, d, steps, warm)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": steps, "warmup": warm, "ms_per_step": cb["seconds_hot_path"] * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": workload_name(n, k, d), "sample": cb["sample"]},
+            "cpu_baseline": {kk: cb[kk] for kk in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+# --------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 3)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    import bsp_gen
+    import bspgemm
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    warmup = max(args.warmup, 3)
+    n, k, d, kind = WORKLOADS[args.workload]
+    G = n // k
+
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        ctx = bspgemm.Context(local, stream=stream.cuda_stream)
+        a = bsp_gen.random_matrix(n, n, k, d, 1000 + 7919 * rank, kind)  # this rank's row panel of A
+        b = bsp_gen.random_matrix(n, n, k, d, 1001, kind)               # B, replicated
+        A, B = ctx.matrix_from_coo(*a), ctx.matrix_from_coo(*b)
+
+        def barrier():
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+
+        st = bspgemm.Stats()
+        for _ in range(warmup):
+            ctx.helper(A, B, stats=st).free()
+        barrier()
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        launches0 = ctx.launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        num_ms, sym_ms = [], []
+        ev0.record(stream)
+        for _ in range(args.steps):
+            ctx.helper(A, B, stats=st).free()
+            num_ms.append(st.ms_numeric); sym_ms.append(st.ms_symbolic)
+        ev1.record(stream)
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        launches = ctx.launch_count() - launches0
+        ms_total = ev0.elapsed_time(ev1)
+        t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+        work = torch.tensor([float(st.nprod)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(work, op=dist.ReduceOp.SUM)
+        ms_step = t.item() / args.steps
+        nprod_all = work.item()
+        value = 2.0 * k ** 3 * nprod_all / (ms_step * 1e-3) / 1e9
+
+        # end to end through the C ABI with HOST buffers: upload A and B, multiply, download C
+        e2e = None
+        if not args.no_e2e:
+            nc = int(st.nnzb_c)
+            pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)  # noqa: E731
+            ha = [pin(a[3].shape, torch.int32), pin(a[4].shape, torch.int32), pin(a[5].size, torch.int64)]
+            hb = [pin(b[3].shape, torch.int32), pin(b[4].shape, torch.int32), pin(b[5].size, torch.int64)]
+            ho = [pin((nc,), torch.int32), pin((nc,), torch.int32), pin((nc * k * k,), torch.int64)]
+            ha[0].numpy()[:] = a[3]; ha[1].numpy()[:] = a[4]; ha[2].numpy().view(np.uint64)[:] = a[5].reshape(-1)
+            hb[0].numpy()[:] = b[3]; hb[1].numpy()[:] = b[4]; hb[2].numpy().view(np.uint64)[:] = b[5].reshape(-1)
+            out = (ho[0].numpy(), ho[1].numpy(), ho[2].numpy().view(np.uint64).reshape(nc, k, k))
+            av = (n, n, ha[0].numpy(), ha[1].numpy(), ha[2].numpy().view(np.uint64))
+            bv = (n, n, hb[0].numpy(), hb[1].numpy(), hb[2].numpy().view(np.uint64))
+            esteps = args.e2e_steps or min(args.steps, 3)
+            ctx.multiply_host(k, av, bv, out=out)  # warm-up
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(esteps):
+                ctx.multiply_host(k, av, bv, out=out)
+            torch.cuda.synchronize()
+            dt = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            e_ms = dt.item() / esteps
+            h2d = sum(x.numel() * x.element_size() for x in ha + hb)
+            d2h = sum(x.numel() * x.element_size() for x in ho)
+            e2e = {"value": 2.0 * k ** 3 * nprod_all / (e_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e_ms,
+                   "steps": esteps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "api": "bsp_multiply_host (pinned host buffers in, pinned host buffers out)"}
+            del ha, hb, ho
+
+        if rank == 0:
+            peak, peak_src = measured_peak()
+            alg = algorithmic_bytes(st.nnzb_a, st.nnzb_b, st.nnzb_c, G, k)
+            k_ms = sum(num_ms) / len(num_ms)
+            s_ms = sum(sym_ms) / len(sym_ms)
+            ach = alg / (k_ms * 1e-3) / 1e9
+            sb = symbolic_bytes(st.nnzb_a, st.nprod, st.nnzb_c, G)
+            line = {
+                "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u64", "data": "synthetic",
+                "config": {"workload": workload_name(n, k, d), "parallelism": "row-panel x%d (B replicated, no collective)" % world,
+                           "l2": "inputs (%.2f GB) and output (%.2f GB per step) exceed the 126 MB L2; no explicit flush"
+                                 % ((st.nnzb_a + st.nnzb_b) * k * k * 8 / 1e9, st.nnzb_c * k * k * 8 / 1e9),
+                           "nnzb_a": st.nnzb_a, "nnzb_b": st.nnzb_b, "nnzb_c": st.nnzb_c, "nprod": st.nprod,
+                           "numeric_path": st.numeric_path, "exact_refolds": st.exact_refolds},
+                "phases_ms": {"symbolic": s_ms, "numeric": k_ms},
+                "roofline": {"bound": "hbm", "kernel": "numeric pass (tile multiply-accumulate)", "achieved": ach,
+                             "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                             "algorithmic_bytes": alg, "peak_source": peak_src,
+                             "useful_u64_mac_per_s": k ** 3 * st.nprod / (k_ms * 1e-3)},
+                "roofline_symbolic": {"bound": "hbm", "achieved": sb / (s_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                      "frac": sb / (s_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes": sb},
+                "gpu_launches": int(launches), "clocks": clocks,
+            }
+            if e2e:
+                line["e2e"] = e2e
+            if world == 1 and not args.no_cpu:
+                try:
+                    cb = cpu_reference_measure(n, k, d, steps=1, warmup=0)
+                    line["cpu_baseline"] = {kk: cb[kk] for kk in ("value", "unit", "cores", "kind", "sample")}
+                except Exception as ex:  # the baseline is reported, never load-bearing
+                    line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(ex)}
+            print(json.dumps(line))
+        A.free(); B.free()
+        ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
