@@ -137,6 +137,24 @@ int bsp_multiply_host(bsp_ctx *ctx, int32_t k,
                       int64_t cap_c, int64_t *nnzb_c, int32_t *brow_c, int32_t *bcol_c,
                       uint64_t *vals_c, bsp_stats *stats);
 
+/* The same compaction as bsp_prune_zero for callers that must not allocate device memory:
+ * processes that gave all of the GPU's memory to their own arena at start-up, or that cannot
+ * afford the device-wide stall of cudaMalloc/cudaFree inside a latency-bound loop.  Has no
+ * counterpart in the reference.  The caller passes the input CSR-of-blocks arrays and output
+ * arrays it already owns (d_colidx_out / d_vals_out sized for nnzb tiles, d_rowptr_out for
+ * nbrows+1 entries, none aliasing an input); *nnzb_out receives the number of tiles kept.
+ * The flags and positions the compaction needs live in an array built into the library
+ * (about 8 MiB, resident on every GPU that loads the library until the process exits), so the
+ * call performs no cudaMalloc, cudaFree or pool allocation.  At most BSP_NOALLOC_MAX_TILES
+ * tiles; more returns BSP_ERR_LIMIT.  All calls on one GPU share that array: do not let two of
+ * them overlap on the device (they race).  The first call on each GPU looks up the array's
+ * address; make it before starting any stream capture. */
+#define BSP_NOALLOC_MAX_TILES (1 << 20)
+int bsp_prune_zero_noalloc(bsp_ctx *ctx, int32_t k, int32_t nbrows, int64_t nnzb,
+                           const int32_t *d_rowptr, const int32_t *d_colidx, const uint64_t *d_vals,
+                           int32_t *d_rowptr_out, int32_t *d_colidx_out, uint64_t *d_vals_out,
+                           int64_t *nnzb_out);
+
 /* ---- text format of the reference (either side of the path) -------------------------- */
 
 /* Parse one "matrixI" file (rows cols / blocks / {brow bcol / k*k values}), cu:345-383. */

@@ -62,6 +62,8 @@ _SIGNATURES = {
                                     C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP,
                                     C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP,
                                     C.c_int64, C.POINTER(C.c_int64), _VP, _VP, _VP, C.POINTER(Stats)]),
+    "bsp_prune_zero_noalloc": (C.c_int, [_VP, C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP, _VP, _VP, _VP,
+                                         C.POINTER(C.c_int64)]),
     "bsp_mat_read_text": (C.c_int, [_VP, C.c_char_p, C.c_int32, C.POINTER(_VP)]),
     "bsp_mat_write_text": (C.c_int, [_VP, _VP, C.c_char_p]),
 }
@@ -239,6 +241,15 @@ class Context:
         return (out, buf.value.decode()) if want_log else out
 
     chain = helper2
+
+    def prune_zero_noalloc(self, k, nbrows, nnzb, d_rowptr, d_colidx, d_vals, d_rowptr_out, d_colidx_out, d_vals_out):
+        """Zero-tile compaction that allocates nothing (raw device addresses in and out; the
+        caller owns every buffer). Returns the number of tiles kept. See include/bspgemm.h for
+        the size limit and the no-overlap rule."""
+        n = C.c_int64(0)
+        self._ck(self.lib.bsp_prune_zero_noalloc(self.handle, k, nbrows, nnzb, d_rowptr, d_colidx, d_vals,
+                                                 d_rowptr_out, d_colidx_out, d_vals_out, C.byref(n)))
+        return n.value
 
     def multiply_host(self, k, a, b, out=None, stats=None):
         """Host buffers in, host buffers out in one C-ABI call. a, b = (rows, cols, brow, bcol, vals).
