@@ -1,4 +1,5 @@
 // bsp_capi.cu -- the extern "C" boundary declared in include/bspgemm.h.
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -60,6 +61,7 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     float ms01 = 0, ms12 = 0;
     BSP_CUDA(ctx, cudaEventElapsedTime(&ms01, ctx->ev[0], ctx->ev[1]));
     BSP_CUDA(ctx, cudaEventElapsedTime(&ms12, ctx->ev[1], ctx->ev[2]));
+    if (st.numeric_path != 0) st.exact_refolds = (int64_t) * (unsigned long long *)((char *)ctx->pinned + 64);
     st.nnzb_c = sym.nnzb_c; st.nprod = sym.nprod;
     st.ms_symbolic = ms01; st.ms_numeric = ms12; st.ms_total = ms01 + ms12;
     st.launches = ctx->launches - launches0;
@@ -123,6 +125,13 @@ int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
     for (int i = 0; i < 4; i++) BSP_CUDA(ctx, cudaEventCreate(&ctx->ev[i]));
     ctx->pinned_bytes = 4096;
     BSP_CUDA(ctx, cudaMallocHost(&ctx->pinned, ctx->pinned_bytes));
+    memset(ctx->pinned, 0, ctx->pinned_bytes);
+    BSP_CUDA(ctx, cudaMalloc(&ctx->d_counters, 256));
+    BSP_CUDA(ctx, cudaMemset(ctx->d_counters, 0, 256));
+    {
+        const char *fg = getenv("BSP_FORCE_GENERIC");
+        ctx->force_generic = fg && fg[0] == '1';
+    }
     // keep freed blocks in the stream-ordered pool: a chain allocates and frees every product
     cudaMemPool_t pool;
     BSP_CUDA(ctx, cudaDeviceGetDefaultMemPool(&pool, device));
@@ -138,6 +147,7 @@ void bsp_ctx_destroy(bsp_ctx *ctx)
     for (int i = 0; i < 4; i++)
         if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->d_counters) cudaFree(ctx->d_counters);
     if (ctx->owns_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

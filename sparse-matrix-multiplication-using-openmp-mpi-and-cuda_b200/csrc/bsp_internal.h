@@ -25,6 +25,8 @@ struct bsp_ctx {
     cudaEvent_t ev[4];
     void *pinned;        // small pinned staging area for scalar read-backs
     size_t pinned_bytes;
+    void *d_counters;    // 256 B of device counters (exact-refold count of the numeric pass)
+    bool force_generic;  // BSP_FORCE_GENERIC=1: always use the any-k exact numeric kernel (tests)
     char err[512];
 };
 

@@ -263,3 +263,32 @@ def test_full_size_chain_is_associative_without_edge_hits(ctx):
     r3 = left.to_coo()
     for x, y, z in zip(r1, r2, r3):
         assert np.array_equal(x, y) and np.array_equal(x, z)
+
+
+@pytest.mark.parametrize("k,kind", [(4, "edgy"), (8, "edgy"), (4, "u64"), (8, "u64")])
+def test_dense_patterns_many_pairs_per_tile(ctx, k, kind):
+    """Every output tile folds dozens of pairs (a dense chain level); with 'edgy' values the
+    2^64-1 detector of the fast path fires on most rows and the exact refold takes over."""
+    G = 37
+    a = bsp_gen.random_matrix(G * k, G * k, k, 0.9, 61, kind)
+    b = bsp_gen.random_matrix(G * k, G * k, k, 0.85, 62, kind)
+    st = bspgemm.Stats()
+    c = ctx.helper(dev(ctx, a), dev(ctx, b), stats=st)
+    assert_same(c, orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))[0])
+    assert st.numeric_path == k
+    if kind == "edgy":
+        assert st.exact_refolds > 0
+
+
+def test_skewed_pairs_per_tile(ctx):
+    """One block row of A hits every row of B (thousands of pairs for its tiles), the others hit
+    one or two: the pair-space work split must still give every tile to exactly one group."""
+    k, G = 8, 200
+    rng = np.random.default_rng(3)
+    br = np.concatenate([np.zeros(G, np.int32), rng.integers(1, G, 300).astype(np.int32)])
+    bc = np.concatenate([np.arange(G, dtype=np.int32), rng.integers(0, G, 300).astype(np.int32)])
+    va = bsp_gen.values(71, br.size * k * k, "u64")
+    a = (G * k, G * k, k, br, bc, va)
+    b = bsp_gen.random_matrix(G * k, G * k, k, 0.3, 72, "u64")
+    c = ctx.helper(dev(ctx, a), dev(ctx, b))
+    assert_same(c, orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))[0])
