@@ -19,6 +19,8 @@
 // HBM-bound integer work; algorithmic bytes:
 //   4*nnzb(A) + 4*nprod + 4*nnzb(C) + 12*(nbr+1), plus the pair lists this design adds:
 //   8*nprod + 8*(nnzb(C)+1).
+#include <cstdlib>
+
 #include "bsp_internal.h"
 
 namespace {
@@ -95,88 +97,268 @@ sym_count_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t 
     }
 }
 
-__global__ void __launch_bounds__(SYM_THREADS)
-sym_fill_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t *__restrict__ a_colidx, int b_nbr,
-                const int32_t *__restrict__ b_rowptr, const int32_t *__restrict__ b_colidx, int words,
-                const int32_t *__restrict__ c_rowptr, const int64_t *__restrict__ row_prod_ptr,
-                int32_t *__restrict__ c_colidx, unsigned long long *pair_ptr /* zeroed, [nnzb_c+1] */,
-                int2 *__restrict__ pairs)
+// ---- fill, shared-memory variant: one CTA per block row of C ----------------------------------
+// Everything the row needs lives in shared memory: the column bitmap and its rank table, one
+// counter per output tile, and the row's whole pair list (8 B per tile product).  Pairs are
+// placed in ascending j by walking the A row entry by entry with the whole CTA spread over
+// B row j (inside one j every target tile is distinct, so the cursor bump needs no atomic),
+// then streamed to global memory with coalesced stores -- DRAM sees each pair exactly once.
+constexpr int FILL_THREADS = 256;
+
+__device__ __forceinline__ int block_excl_scan_i32(int v, int *sm33, int *total)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
+    }
+    if (lane == 31) sm33[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < nwarp ? sm33[lane] : 0;
+        int ws = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int o = __shfl_up_sync(0xffffffffu, ws, d);
+            if (lane >= d) ws += o;
+        }
+        sm33[lane] = ws - w;
+        if (lane == 31) sm33[32] = ws;
+    }
+    __syncthreads();
+    const int res = inc - v + sm33[warp];
+    *total = sm33[32];
+    __syncthreads();
+    return res;
+}
+
+__global__ void __launch_bounds__(FILL_THREADS)
+sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
+                     const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
+                     const int32_t *__restrict__ b_colidx, int words, int pcap,
+                     const int32_t *__restrict__ c_rowptr, const int64_t *__restrict__ row_prod_ptr,
+                     int32_t *__restrict__ c_colidx, int64_t *__restrict__ pair_ptr, int2 *__restrict__ pairs)
 {
     extern __shared__ uint32_t smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t *bm = smem + (size_t)warp * 2 * words;
+    __shared__ int sm33[33];
+    uint32_t *bm = smem;
     uint32_t *wrank = bm + words;
-    for (int row = blockIdx.x * SYM_WARPS + warp; row < a_nbr; row += gridDim.x * SYM_WARPS) {
-        const int cbase = c_rowptr[row], cend = c_rowptr[row + 1];
-        if (cend == cbase) continue; // warp-uniform
-        build_row_bitmap(bm, words, a_rowptr, a_colidx, b_nbr, b_rowptr, b_colidx, row);
-        // word-level exclusive prefix of popcounts: rank(c) = wrank[c>>5] + popc(bits below c)
-        int carry = 0;
-        for (int w0 = 0; w0 < words; w0 += 32) {
-            const int w = w0 + lane;
-            const uint32_t bits = w < words ? bm[w] : 0u;
-            int tot;
-            const int ex = warp_excl_scan(__popc(bits), &tot);
-            if (w < words) {
-                wrank[w] = (uint32_t)(carry + ex);
-                // sorted, duplicate-free block columns of C row
-                uint32_t b = bits;
-                int o = cbase + carry + ex;
-                while (b) {
-                    const int bit = __ffs(b) - 1;
-                    b &= b - 1;
-                    c_colidx[o++] = w * 32 + bit;
-                }
-            }
-            carry += tot;
+    int *cur = (int *)(wrank + words);                          // [pcap + 2] per-tile counter, then cursor
+    int2 *sp = (int2 *)(cur + ((pcap + 2 + 1) & ~1));           // [pcap] the row's pairs
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = FILL_THREADS / 32;
+    const int row = rowlist[blockIdx.x];
+    const int cbase = c_rowptr[row], T = c_rowptr[row + 1] - cbase;
+    const int64_t pbase = row_prod_ptr[row];
+    const int P = (int)(row_prod_ptr[row + 1] - pbase);
+    const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
+
+    for (int w = tid; w < words; w += FILL_THREADS) bm[w] = 0u;
+    for (int t = tid; t < T + 1; t += FILL_THREADS) cur[t] = 0;
+    __syncthreads();
+    // 1. bitmap of reachable block columns (warps over A entries, lanes over B row j)
+    for (int p = a0 + warp; p < a1; p += nwarp) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            atomicOr(&bm[c >> 5], 1u << (c & 31));
         }
-        __syncwarp();
-        // pairs per output tile, counted at pair_ptr[tile+1]
-        const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
-        for (int p = a0; p < a1; p++) {
-            const int j = a_colidx[p];
-            if (j >= b_nbr) continue;
-            const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
-            for (int q = b0 + lane; q < b1; q += 32) {
-                const int c = b_colidx[q];
-                const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
-                atomicAdd(&pair_ptr[(size_t)cbase + t + 1], 1ull);
+    }
+    __syncthreads();
+    // 2. rank table + sorted colidx of the C row
+    int carry = 0;
+    for (int w0 = 0; w0 < words; w0 += FILL_THREADS) {
+        const int w = w0 + tid;
+        const uint32_t bits = w < words ? bm[w] : 0u;
+        int tot;
+        const int ex = block_excl_scan_i32(__popc(bits), sm33, &tot);
+        if (w < words) {
+            wrank[w] = (uint32_t)(carry + ex);
+            uint32_t b = bits;
+            int o = cbase + carry + ex;
+            while (b) {
+                const int bit = __ffs(b) - 1;
+                b &= b - 1;
+                c_colidx[o++] = w * 32 + bit;
             }
         }
-        __syncwarp();
-        // in-place exclusive scan of the row's counts: pair_ptr[tile+1] = first slot of tile
-        // (it is advanced while filling and ends as the first slot of tile+1, i.e. the CSR pointer)
+        carry += tot;
+    }
+    __syncthreads();
+    // 3. pairs per output tile
+    for (int p = a0 + warp; p < a1; p += nwarp) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+            atomicAdd(&cur[t], 1);
+        }
+    }
+    __syncthreads();
+    // 4. exclusive scan -> first slot of every tile; publish pair_ptr; cur[] becomes the cursor
+    carry = 0;
+    for (int t0 = 0; t0 < T; t0 += FILL_THREADS) {
+        const int t = t0 + tid;
+        const int v = t < T ? cur[t] : 0;
+        int tot;
+        const int ex = block_excl_scan_i32(v, sm33, &tot);
+        if (t < T) {
+            cur[t] = carry + ex;
+            pair_ptr[(size_t)cbase + t] = pbase + carry + ex;
+        }
+        carry += tot;
+    }
+    __syncthreads();
+    // 5. ordered placement: A row in ascending j, the CTA over B row j
+    for (int p = a0; p < a1; p++) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue; // uniform
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        for (int q = b0 + tid; q < b1; q += FILL_THREADS) {
+            const int c = b_colidx[q];
+            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+            const int pos = cur[t];
+            cur[t] = pos + 1;
+            sp[pos] = make_int2(p, q);
+        }
+        __syncthreads();
+    }
+    // 6. stream the row's pairs out
+    for (int x = tid; x < P; x += FILL_THREADS) pairs[pbase + x] = sp[x];
+}
+
+// ---- fill, global-memory variant: rows whose pair list does not fit in shared memory ----------
+// Same algorithm with the per-tile counters/cursors kept in the row's own pair_ptr slots: slot t
+// holds the count, then the first free slot of tile t; after the placement it holds the END of
+// tile t, and a final in-row shift turns ends into starts.  A row touches only its own slots.
+constexpr int FILLG_THREADS = 512;
+
+__global__ void __launch_bounds__(FILLG_THREADS)
+sym_fill_global_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
+                       const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
+                       const int32_t *__restrict__ b_colidx, int words, const int32_t *__restrict__ c_rowptr,
+                       const int64_t *__restrict__ row_prod_ptr, int32_t *__restrict__ c_colidx,
+                       unsigned long long *pair_ptr, int2 *__restrict__ pairs)
+{
+    extern __shared__ uint32_t smem[];
+    __shared__ int sm33[33];
+    uint32_t *bm = smem;
+    uint32_t *wrank = bm + words;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = FILLG_THREADS / 32;
+    const int row = rowlist[blockIdx.x];
+    const int cbase = c_rowptr[row], cend = c_rowptr[row + 1], T = cend - cbase;
+    const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
+    for (int w = tid; w < words; w += FILLG_THREADS) bm[w] = 0u;
+    for (int t = tid; t < T; t += FILLG_THREADS) pair_ptr[(size_t)cbase + t] = 0ull;
+    __syncthreads();
+    for (int p = a0 + warp; p < a1; p += nwarp) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            atomicOr(&bm[c >> 5], 1u << (c & 31));
+        }
+    }
+    __syncthreads();
+    int carry = 0;
+    for (int w0 = 0; w0 < words; w0 += FILLG_THREADS) {
+        const int w = w0 + tid;
+        const uint32_t bits = w < words ? bm[w] : 0u;
+        int tot;
+        const int ex = block_excl_scan_i32(__popc(bits), sm33, &tot);
+        if (w < words) {
+            wrank[w] = (uint32_t)(carry + ex);
+            uint32_t b = bits;
+            int o = cbase + carry + ex;
+            while (b) {
+                const int bit = __ffs(b) - 1;
+                b &= b - 1;
+                c_colidx[o++] = w * 32 + bit;
+            }
+        }
+        carry += tot;
+    }
+    __syncthreads();
+    for (int p = a0 + warp; p < a1; p += nwarp) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+            atomicAdd(&pair_ptr[(size_t)cbase + t], 1ull);
+        }
+    }
+    __threadfence_block();
+    __syncthreads();
+    // in-place exclusive scan of the row's counts by warp 0 (rows this large are rare)
+    if (warp == 0) {
         unsigned long long run = (unsigned long long)row_prod_ptr[row];
-        for (int t0 = cbase; t0 < cend; t0 += 32) {
+        for (int t0 = 0; t0 < T; t0 += 32) {
             const int t = t0 + lane;
-            const unsigned long long v = t < cend ? pair_ptr[(size_t)t + 1] : 0ull;
+            const unsigned long long v = t < T ? pair_ptr[(size_t)cbase + t] : 0ull;
             unsigned long long inc = v;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
                 if (lane >= d) inc += o;
             }
-            if (t < cend) pair_ptr[(size_t)t + 1] = run + inc - v;
+            if (t < T) pair_ptr[(size_t)cbase + t] = run + inc - v;
             run += __shfl_sync(0xffffffffu, inc, 31);
         }
-        __syncwarp();
-        // ordered append: A row walked in ascending j; lanes over B row j (distinct tiles)
-        for (int p = a0; p < a1; p++) {
-            const int j = a_colidx[p];
-            if (j >= b_nbr) continue;
-            const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
-            for (int q = b0 + lane; q < b1; q += 32) {
-                const int c = b_colidx[q];
-                const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
-                volatile unsigned long long *cur = &pair_ptr[(size_t)cbase + t + 1];
-                const unsigned long long pos = *cur;
-                *cur = pos + 1ull;
-                pairs[pos] = make_int2(p, q);
-            }
-            __syncwarp();
-        }
-        __syncwarp();
     }
+    __threadfence_block();
+    __syncthreads();
+    for (int p = a0; p < a1; p++) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        for (int q = b0 + tid; q < b1; q += FILLG_THREADS) {
+            const int c = b_colidx[q];
+            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+            volatile unsigned long long *cu = &pair_ptr[(size_t)cbase + t];
+            const unsigned long long pos = *cu;
+            *cu = pos + 1ull;
+            pairs[pos] = make_int2(p, q);
+        }
+        __threadfence_block();
+        __syncthreads();
+    }
+    // slots now hold tile ends; shift by one inside the row (last chunk first) to get tile starts
+    const int nchunk = (T + FILLG_THREADS - 1) / FILLG_THREADS;
+    for (int ch = nchunk - 1; ch >= 0; ch--) {
+        const int t = ch * FILLG_THREADS + tid;
+        unsigned long long prev = 0ull;
+        if (t < T) prev = t == 0 ? (unsigned long long)row_prod_ptr[row]
+                                 : ((volatile unsigned long long *)pair_ptr)[(size_t)cbase + t - 1];
+        __syncthreads();
+        if (t < T) pair_ptr[(size_t)cbase + t] = prev;
+        __threadfence_block();
+        __syncthreads();
+    }
+}
+
+// ---- rows -> capacity classes -----------------------------------------------------------------
+// class c rows go to lists[c * nbr ...]; counts[c] = rows in class c.  A row with P tile
+// products fits class c when P <= caps[c]; larger than every cap -> class NCLASS-1 (global).
+constexpr int NCLASS = 4;
+
+__global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ row_cnt, const int32_t *__restrict__ row_prod,
+                                     int cap0, int cap1, int cap2, int32_t *__restrict__ lists,
+                                     int32_t *__restrict__ counts)
+{
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nbr || row_cnt[row] == 0) return;
+    const int P = row_prod[row];
+    const int cls = P <= cap0 ? 0 : (P <= cap1 ? 1 : (P <= cap2 ? 2 : 3));
+    const int slot = atomicAdd(&counts[cls], 1);
+    lists[(size_t)cls * nbr + slot] = row;
 }
 
 } // namespace
@@ -188,30 +370,46 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     const int nbr = A->nbr;
     const int words = (B->nbc + 31) / 32 > 0 ? (B->nbc + 31) / 32 : 1;
     const size_t smem_count = (size_t)SYM_WARPS * words * sizeof(uint32_t);
-    const size_t smem_fill = 2 * smem_count;
-    if (smem_fill > 200 * 1024)
+    const size_t bitmap_bytes = 2 * (size_t)words * sizeof(uint32_t);
+    if (smem_count > 200 * 1024)
         BSP_FAIL(ctx, BSP_ERR_LIMIT,
                  "symbolic pass: block-column space %d needs %zu B of shared memory per CTA (limit 204800 B, "
-                 "i.e. at most 102400 block columns)", B->nbc, smem_fill);
+                 "i.e. at most 204800 block columns)", B->nbc, smem_count);
 
-    int32_t *row_cnt = nullptr, *row_prod = nullptr;
+    int32_t *row_cnt = nullptr, *row_prod = nullptr, *lists = nullptr, *counts = nullptr;
     int64_t *row_prod_ptr = nullptr;
     BSP_TRY(bsp_alloc(ctx, &row_cnt, (size_t)nbr + 1));
     BSP_TRY(bsp_alloc(ctx, &row_prod, (size_t)nbr + 1));
     BSP_TRY(bsp_alloc(ctx, &row_prod_ptr, (size_t)nbr + 1));
+    BSP_TRY(bsp_alloc(ctx, &lists, (size_t)NCLASS * (nbr > 0 ? nbr : 1)));
+    BSP_TRY(bsp_alloc(ctx, &counts, (size_t)NCLASS));
     BSP_TRY(bsp_alloc(ctx, &out->c_rowptr, (size_t)nbr + 1));
     BSP_CUDA(ctx, cudaMemsetAsync(row_cnt + nbr, 0, sizeof(int32_t), ctx->stream));
     BSP_CUDA(ctx, cudaMemsetAsync(row_prod + nbr, 0, sizeof(int32_t), ctx->stream));
+    BSP_CUDA(ctx, cudaMemsetAsync(counts, 0, NCLASS * sizeof(int32_t), ctx->stream));
 
     int grid = (nbr + SYM_WARPS - 1) / SYM_WARPS;
     const int max_grid = ctx->sm_count * 8;
     if (grid > max_grid) grid = max_grid;
     if (grid < 1) grid = 1;
+    // capacity classes of the shared-memory fill: tile products per row that fit next to the bitmaps
+    //   bytes(pcap) = 8*words + 4*(pcap+3) + 8*pcap
+    auto fill_bytes = [&](int pcap) { return bitmap_bytes + 4 * ((size_t)pcap + 4) + 8 * (size_t)pcap; };
+    int caps[3] = {1536, 8192, 16384};
+    if (const char *e = getenv("BSP_SYM_CAPS")) { // test hook: force rows into the larger classes
+        int a, b, c;
+        if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && a <= b && b <= c) { caps[0] = a; caps[1] = b; caps[2] = c; }
+    }
+    for (int c = 0; c < 3; c++)
+        while (caps[c] > 0 && fill_bytes(caps[c]) > 220 * 1024) caps[c] /= 2;
     if (nbr > 0) {
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)smem_count));
         sym_count_kernel<<<grid, SYM_THREADS, smem_count, ctx->stream>>>(
             nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, row_lo, row_hi, row_cnt, row_prod);
+        BSP_LAUNCH_CHECK(ctx);
+        classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, row_cnt, row_prod, caps[0], caps[1],
+                                                                        caps[2], lists, counts);
         BSP_LAUNCH_CHECK(ctx);
     }
     BSP_TRY(bsp_scan_i32(ctx, row_cnt, out->c_rowptr, (int64_t)nbr + 1, nullptr));
@@ -220,27 +418,44 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     // totals -> host (the one unavoidable sync of the pass: C and the pair lists are sized from them)
     int32_t *h_nnzb = (int32_t *)ctx->pinned;
     int64_t *h_nprod = (int64_t *)((char *)ctx->pinned + 8);
+    int32_t *h_counts = (int32_t *)((char *)ctx->pinned + 16);
     BSP_CUDA(ctx, cudaMemcpyAsync(h_nnzb, out->c_rowptr + nbr, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
     BSP_CUDA(ctx, cudaMemcpyAsync(h_nprod, row_prod_ptr + nbr, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    BSP_CUDA(ctx, cudaMemcpyAsync(h_counts, counts, NCLASS * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     out->nnzb_c = *h_nnzb;
     out->nprod = *h_nprod;
+    int ncls[NCLASS];
+    for (int c = 0; c < NCLASS; c++) ncls[c] = h_counts[c];
     if (out->nnzb_c < 0) BSP_FAIL(ctx, BSP_ERR_LIMIT, "product has more than 2^31-1 tiles");
 
     BSP_TRY(bsp_alloc(ctx, &out->c_colidx, (size_t)out->nnzb_c));
     BSP_TRY(bsp_alloc(ctx, &out->pair_ptr, (size_t)out->nnzb_c + 1));
     BSP_TRY(bsp_alloc(ctx, &out->pairs, (size_t)out->nprod));
-    BSP_CUDA(ctx, cudaMemsetAsync(out->pair_ptr, 0, ((size_t)out->nnzb_c + 1) * sizeof(int64_t), ctx->stream));
-    if (out->nnzb_c > 0) {
-        BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)smem_fill));
-        sym_fill_kernel<<<grid, SYM_THREADS, smem_fill, ctx->stream>>>(
-            nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, out->c_rowptr, row_prod_ptr,
-            out->c_colidx, (unsigned long long *)out->pair_ptr, out->pairs);
+    // every row writes its own slots; the closing entry pair_ptr[nnzb_c] = nprod comes from the row scan
+    BSP_CUDA(ctx, cudaMemcpyAsync(out->pair_ptr + out->nnzb_c, row_prod_ptr + nbr, sizeof(int64_t),
+                                  cudaMemcpyDeviceToDevice, ctx->stream));
+    for (int c = 0; c < 3; c++) {
+        if (ncls[c] == 0) continue;
+        const size_t bytes = fill_bytes(caps[c]);
+        BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        sym_fill_smem_kernel<<<ncls[c], FILL_THREADS, bytes, ctx->stream>>>(
+            lists + (size_t)c * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, caps[c], out->c_rowptr,
+            row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
+        BSP_LAUNCH_CHECK(ctx);
+    }
+    if (ncls[3] > 0) {
+        BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)bitmap_bytes));
+        sym_fill_global_kernel<<<ncls[3], FILLG_THREADS, bitmap_bytes, ctx->stream>>>(
+            lists + (size_t)3 * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, out->c_rowptr,
+            row_prod_ptr, out->c_colidx, (unsigned long long *)out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
     bsp_release(ctx, row_cnt);
     bsp_release(ctx, row_prod);
     bsp_release(ctx, row_prod_ptr);
+    bsp_release(ctx, lists);
+    bsp_release(ctx, counts);
     return BSP_OK;
 }

@@ -292,3 +292,25 @@ def test_skewed_pairs_per_tile(ctx):
     b = bsp_gen.random_matrix(G * k, G * k, k, 0.3, 72, "u64")
     c = ctx.helper(dev(ctx, a), dev(ctx, b))
     assert_same(c, orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))[0])
+
+
+def test_symbolic_row_classes_and_generic_numeric(ctx):
+    """Force rows through every capacity class of the symbolic fill (shared-memory classes and
+    the global-memory variant) and through the any-k exact numeric kernel; all must agree."""
+    import os
+    k = 4
+    a = bsp_gen.random_matrix(160 * k, 160 * k, k, 0.15, 81, "edgy")
+    b = bsp_gen.random_matrix(160 * k, 160 * k, k, 0.2, 82, "edgy")
+    ref = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))[0]
+    try:
+        for caps in ("16,64,256", "4,8,16", "100000,100000,100000"):
+            os.environ["BSP_SYM_CAPS"] = caps
+            assert_same(ctx.helper(dev(ctx, a), dev(ctx, b)), ref)
+        os.environ["BSP_FORCE_GENERIC"] = "1"
+        with bspgemm.Context(0) as c2:
+            st = bspgemm.Stats()
+            assert_same(c2.helper(c2.matrix_from_coo(*a), c2.matrix_from_coo(*b), stats=st), ref)
+            assert st.numeric_path == 0
+    finally:
+        os.environ.pop("BSP_SYM_CAPS", None)
+        os.environ.pop("BSP_FORCE_GENERIC", None)
