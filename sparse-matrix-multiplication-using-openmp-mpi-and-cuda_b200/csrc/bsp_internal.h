@@ -98,7 +98,8 @@ struct bsp_symbolic_out {
     int32_t *c_rowptr;   // [nbr+1]
     int32_t *c_colidx;   // [nnzb_c]
     int64_t *pair_ptr;   // [nnzb_c+1]
-    int2 *pairs;         // [nprod]  (index of A tile, index of B tile), ascending inner block index
+    int2 *pairs;         // [nprod]  (index of A tile, index of B tile | sign bit on the last pair of a tile),
+                         //          ascending inner block index inside a tile
     int64_t nnzb_c;
     int64_t nprod;
 };

@@ -51,7 +51,7 @@ __device__ __forceinline__ uint64_t fold_exact(const uint64_t *__restrict__ a_va
     for (int64_t p = p0; p < p1; p++) {
         const int2 pr = pairs[p];
         const uint64_t *A = a_vals + (size_t)pr.x * kk + (size_t)r * k;
-        const uint64_t *B = b_vals + (size_t)pr.y * kk + c;
+        const uint64_t *B = b_vals + (size_t)(pr.y & 0x7fffffff) * kk + c; // sign bit = last pair of the tile
         for (int j = 0; j < k; j++) {
             const uint64_t t = phi(A[j] * B[(size_t)j * k]);
             acc = phi(acc + t);
@@ -86,35 +86,18 @@ numeric_generic_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__re
 
 // ---- fast path ------------------------------------------------------------------------------
 
-// chunk g = tiles whose first pair index is in [g*Q, (g+1)*Q)
-__global__ void chunk_bounds_kernel(const int64_t *__restrict__ pair_ptr, int64_t nnzb_c, int64_t nprod, int64_t Q,
-                                    int nchunks, int32_t *__restrict__ chunk_tile)
-{
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g > nchunks) return;
-    if (g == nchunks) { chunk_tile[g] = (int32_t)nnzb_c; return; }
-    int64_t target = (int64_t)g * Q;
-    if (target > nprod) target = nprod;
-    int64_t lo = 0, hi = nnzb_c; // first t with pair_ptr[t] >= target
-    while (lo < hi) {
-        const int64_t mid = (lo + hi) >> 1;
-        if (pair_ptr[mid] < target) lo = mid + 1; else hi = mid;
-    }
-    chunk_tile[g] = (int32_t)lo;
-}
-
-// s += a*b (mod 2^64) and the conservative 2^64-1 detector on the low words
+// s += a*b (mod 2^64) and the conservative 2^64-1 detector on the low words.
+// Kept as a plain 64-bit multiply-add: nvcc lowers it to IMAD.WIDE.U32 onto the accumulator
+// + two IMAD for the cross terms + one add into the high word, and the detector to
+// VIADDMNMX (max(lo - lo_old, lo)) + half a VIMNMX3 -- 5.5 integer instructions per step.
+// (Hand-split 32-bit halves, separate cross-term accumulators and PTX mad.wide chains were all
+// tried: ptxas re-associates them into longer sequences with extra register moves.)
 __device__ __forceinline__ void mac_flag(uint64_t &s, uint32_t &flag, uint64_t a, uint64_t b)
 {
-    const uint32_t alo = (uint32_t)a, ahi = (uint32_t)(a >> 32), blo = (uint32_t)b, bhi = (uint32_t)(b >> 32);
     const uint32_t lo_old = (uint32_t)s;
-    const uint64_t t = (uint64_t)alo * blo + s; // IMAD.WIDE.U32
-    uint32_t thi = (uint32_t)(t >> 32);
-    thi = alo * bhi + thi; // IMAD
-    thi = ahi * blo + thi; // IMAD
-    const uint32_t lo = (uint32_t)t;
-    flag = max(flag, max(lo, lo - lo_old)); // VIADDMNMX / VIMNMX3
-    s = ((uint64_t)thi << 32) | lo;
+    s += a * b;
+    const uint32_t lo = (uint32_t)s;
+    flag = max(flag, max(lo, lo - lo_old));
 }
 
 template <int K>
@@ -125,131 +108,371 @@ __device__ __noinline__ void refold_row_exact(const uint64_t *__restrict__ a_val
     for (int c = 0; c < K; c++) out_row[c] = fold_exact(a_vals, b_vals, pairs, p0, p1, K, r, c);
 }
 
-constexpr int ROWS_THREADS = 256;
+// -- chunk schedule ---------------------------------------------------------------------------
+// The block columns of C are cut into `npanels` panels so that the part of B a panel touches
+// (|B| / npanels) stays resident in the 126 MB L2 while all block rows are swept; a segment is
+// (panel, block row) = a contiguous range of output tiles; a chunk is at most Q consecutive tile
+// products of one segment (whole tiles).  Chunks are numbered panel-major, so the CTAs that
+// run together gather from the same panel of B.
 
+__device__ __forceinline__ int lower_bound_i32(const int32_t *__restrict__ a, int lo, int hi, int key)
+{
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (a[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+__device__ __forceinline__ int lower_bound_i64(const int64_t *__restrict__ a, int lo, int hi, int64_t key)
+{
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (a[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void seg_bounds_kernel(int nbr, int npanels, int panel_w, const int32_t *__restrict__ c_rowptr,
+                                  const int32_t *__restrict__ c_colidx, const int64_t *__restrict__ pair_ptr, int Q,
+                                  int32_t *__restrict__ seg_ts, int32_t *__restrict__ seg_nchunks)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nseg = nbr * npanels;
+    if (x > nseg) return;
+    if (x == nseg) { seg_nchunks[x] = 0; seg_ts[x] = c_rowptr[nbr]; return; }
+    const int pnl = x / nbr, row = x - pnl * nbr;
+    const int r0 = c_rowptr[row], r1 = c_rowptr[row + 1];
+    const int ts = pnl == 0 ? r0 : lower_bound_i32(c_colidx, r0, r1, pnl * panel_w);
+    const int te = pnl == npanels - 1 ? r1 : lower_bound_i32(c_colidx, r0, r1, (pnl + 1) * panel_w);
+    seg_ts[x] = ts;
+    const int64_t np = pair_ptr[te] - pair_ptr[ts];
+    seg_nchunks[x] = (int)((np + Q - 1) / Q);
+}
+
+__global__ void chunk_fill_kernel(int nbr, int npanels, int panel_w, const int32_t *__restrict__ c_rowptr,
+                                  const int32_t *__restrict__ c_colidx, const int64_t *__restrict__ pair_ptr, int Q,
+                                  const int32_t *__restrict__ seg_ts, const int32_t *__restrict__ seg_off,
+                                  int2 *__restrict__ chunk_tiles)
+{
+    const int nseg = nbr * npanels;
+    const int total = seg_off[nseg];
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= total) return;
+    // segment of chunk x: last seg with seg_off[seg] <= x
+    int lo = 0, hi = nseg;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (seg_off[mid] <= x) lo = mid; else hi = mid;
+    }
+    const int seg = lo, l = x - seg_off[seg], n = seg_off[seg + 1] - seg_off[seg];
+    const int pnl = seg / nbr, row = seg - pnl * nbr;
+    const int ts = seg_ts[seg];
+    const int r1 = c_rowptr[row + 1];
+    const int te = pnl == npanels - 1 ? r1 : lower_bound_i32(c_colidx, ts, r1, (pnl + 1) * panel_w);
+    const int64_t base = pair_ptr[ts];
+    const int t0 = l == 0 ? ts : lower_bound_i64(pair_ptr, ts, te, base + (int64_t)l * Q);
+    const int t1 = l == n - 1 ? te : lower_bound_i64(pair_ptr, ts, te, base + (int64_t)(l + 1) * Q);
+    chunk_tiles[x] = make_int2(t0, t1);
+}
+
+// -- the kernel -------------------------------------------------------------------------------
+
+__device__ __forceinline__ void cp_async_ca16(void *smem_dst, const void *gsrc)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_cg16(void *smem_dst, const void *gsrc)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// A group of TPT threads owns one output tile at a time; thread h of the group holds rows
+// h, h+TPT, ... (RPT = K/TPT rows, K accumulators each).  Fewer threads per tile means fewer
+// redundant shared-memory reads of the B tile (every thread of a group needs all of it): the
+// first version of this kernel used K threads per tile and spent as long in the shared-memory
+// pipe (56 wavefronts per tile product) as in the integer pipe; K/2 threads per tile halve that.
 template <int K>
 struct RowsCfg {
-    static constexpr int GROUPS = 32 / K;                 // groups per warp
+    static constexpr int TPT = K / 2;                          // threads per output tile
+    static constexpr int RPT = K / TPT;                        // rows per thread (= 2)
+    static constexpr int GROUPS = 32 / TPT;                    // tiles in flight per warp
     static constexpr int TILE_BYTES = K * K * 8;
-    static constexpr int CHUNKS = TILE_BYTES / 16;        // 16-byte chunks per tile
-    static constexpr int CPT = CHUNKS / K;                // chunks each thread moves per tile (= K/2)
-    static constexpr int GROUP_STRIDE = TILE_BYTES + 16;  // +16 B: groups land in different banks
-    static constexpr int BUF_BYTES = GROUPS * GROUP_STRIDE;
-    static constexpr int WARP_BYTES = 2 * BUF_BYTES;      // double buffered
+    static constexpr int CHUNKS = TILE_BYTES / 16;             // 16-byte chunks per tile (32 for k=8, 8 for k=4)
+    static constexpr int TPI = CHUNKS >= 32 ? 1 : 32 / CHUNKS; // tiles moved by one warp-wide cp.async
+    static constexpr int IPT = CHUNKS >= 32 ? CHUNKS / 32 : 1; // warp-wide cp.async instructions per tile
+    static constexpr int GROUP_STRIDE = 2 * TILE_BYTES + 32;   // A tile, B tile; +32 B shifts the next group by 8 banks
+    static constexpr int STAGE_BYTES = GROUPS * GROUP_STRIDE;  // per warp
 };
 
+// position of 16-byte chunk i of row r inside the A tile: XOR swizzle so that the TPT threads
+// of a group (rows h, h+TPT of 64 B each for k=8) read different bank quads with LDS.128
 template <int K>
-__global__ void __launch_bounds__(ROWS_THREADS)
+__device__ __forceinline__ int a_chunk_offset(int r, int i)
+{
+    if (K == 8) return r * 64 + (((i ^ (r >> 1)) & 3) << 4);
+    return r * (K * 8) + i * 16;
+}
+
+__device__ __forceinline__ void cp_async16_ca(unsigned smem_addr, const void *gsrc)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(smem_addr), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16_cg(unsigned smem_addr, const void *gsrc)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_addr), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ ulonglong2 lds128(unsigned smem_addr)
+{
+    ulonglong2 v;
+    asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];\n" : "=l"(v.x), "=l"(v.y) : "r"(smem_addr));
+    return v;
+}
+
+template <int K, int STAGES, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
 numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restrict__ b_vals,
                     const int64_t *__restrict__ pair_ptr, const int2 *__restrict__ pairs,
-                    const int32_t *__restrict__ chunk_tile, int nchunks, uint64_t *__restrict__ c_vals,
-                    unsigned long long *__restrict__ refold_count)
+                    const int2 *__restrict__ chunk_tiles, const int32_t *__restrict__ nchunks_ptr,
+                    uint64_t *__restrict__ c_vals, unsigned long long *__restrict__ refold_count)
 {
     using Cfg = RowsCfg<K>;
-    __shared__ __align__(16) unsigned char smem[(ROWS_THREADS / 32) * Cfg::WARP_BYTES];
+    constexpr int TPT = Cfg::TPT, RPT = Cfg::RPT;
+    constexpr int NCOPY = 2 * Cfg::GROUPS * Cfg::IPT / Cfg::TPI; // warp-wide cp.async instructions per step
+    extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int grp = lane / K, r = lane % K;
-    unsigned char *wbase = smem + warp * Cfg::WARP_BYTES + grp * Cfg::GROUP_STRIDE;
+    const int grp = lane / TPT, h = lane % TPT;
+    // 32-bit shared-memory addresses, computed once
+    const unsigned wbase = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)warp * (STAGES * Cfg::STAGE_BYTES);
 
-    const int g = (blockIdx.x * (ROWS_THREADS / 32) + warp) * Cfg::GROUPS + grp;
-    int t = 0, t_end = 0;
-    if (g < nchunks) { t = chunk_tile[g]; t_end = chunk_tile[g + 1]; }
-    int64_t p = 0, p_end = 0;
-    if (t < t_end) { p = pair_ptr[t]; p_end = pair_ptr[t_end]; }
-    int64_t pe = (t < t_end) ? pair_ptr[t + 1] : 0; // end of the current tile's pairs
-    int steps = (int)(p_end - p);
+    const int nchunks = *nchunks_ptr;
+    const int g = (blockIdx.x * WARPS + warp) * Cfg::GROUPS + grp;
+    int t = 0, n = 0;        // current output tile, tile products (steps) of this group's chunk
+    const int2 *prs = pairs; // this chunk's slice of the pair stream
+    if (g < nchunks) {
+        const int2 ct = chunk_tiles[g];
+        if (ct.x < ct.y) {
+            const int64_t p0 = pair_ptr[ct.x];
+            t = ct.x;
+            n = (int)(pair_ptr[ct.y] - p0);
+            prs = pairs + p0;
+        }
+    }
+    int steps = n;
 #pragma unroll
     for (int d = 16; d; d >>= 1) steps = max(steps, __shfl_xor_sync(0xffffffffu, steps, d));
+    if (steps == 0) return; // warp-uniform
 
-    uint64_t acc[K], a_cur[K], a_nxt[K];
-    ulonglong2 b_nxt[Cfg::CPT];
+    // What this lane moves in each warp-wide cp.async: chunk `cn` of a tile of group
+    // (q0 + cq), to a fixed offset inside the stage (A tiles XOR-swizzled, B tiles as they are).
+    const int cn = Cfg::TPI > 1 ? lane % Cfg::CHUNKS : lane;
+    const int cq = Cfg::TPI > 1 ? lane / Cfg::CHUNKS : 0;
+    const unsigned char *a_lane = reinterpret_cast<const unsigned char *>(a_vals) + cn * 16;
+    const unsigned char *b_lane = reinterpret_cast<const unsigned char *>(b_vals) + cn * 16;
+    unsigned dstA[Cfg::IPT], dstB[Cfg::IPT];
+#pragma unroll
+    for (int part = 0; part < Cfg::IPT; part++) {
+        const int nn = cn + 32 * part;
+        dstA[part] = cq * Cfg::GROUP_STRIDE + a_chunk_offset<K>(nn / (K / 2), nn % (K / 2));
+        dstB[part] = cq * Cfg::GROUP_STRIDE + Cfg::TILE_BYTES + nn * 16;
+    }
+
+    // The whole warp copies the tiles of all its groups for one step into stage ST: every
+    // cp.async instruction moves 512 contiguous bytes (one k=8 tile, or four k=4 tiles).
+    // (ai, bi) = this group's pair for that step.  A group that has run out of steps repeats
+    // its last pair (or tile 0): the bytes land in a stage nobody reads.
+    auto issue = [&](int ST, int ai, int bi) {
+        const unsigned sbase = wbase + ST * Cfg::STAGE_BYTES;
+#pragma unroll
+        for (int q0 = 0; q0 < Cfg::GROUPS; q0 += Cfg::TPI) {
+            const int src_lane = (q0 + cq) * TPT;
+            const int qa = __shfl_sync(0xffffffffu, ai, src_lane);
+            const int qb = __shfl_sync(0xffffffffu, bi, src_lane);
+#pragma unroll
+            for (int part = 0; part < Cfg::IPT; part++) {
+                cp_async16_ca(sbase + q0 * Cfg::GROUP_STRIDE + dstA[part],
+                              a_lane + (size_t)(unsigned)qa * Cfg::TILE_BYTES + part * 512);
+                cp_async16_cg(sbase + q0 * Cfg::GROUP_STRIDE + dstB[part],
+                              b_lane + (size_t)(unsigned)qb * Cfg::TILE_BYTES + part * 512);
+            }
+        }
+    };
+    (void)NCOPY;
+
+    // prologue: fill STAGES-1 stages.  (nx, ny) = pair of the next step to be issued;
+    // lastq bit i = "the pair of step k+i closes its tile" (sign bit set by the symbolic pass)
+    // Pair loads are unconditional (index clamped to the chunk): a predicated load would make
+    // the loop-carried registers wait for it on the spot instead of one step later.
+    const int n_last = max(n - 1, 0);
+    int nx, ny;
+    unsigned lastq = 0;
+    { const int2 pr = __ldcs(prs); nx = pr.x; ny = pr.y; }
+#pragma unroll
+    for (int st = 0; st < STAGES - 1; st++) {
+        issue(st, nx, ny & 0x7fffffff);
+        lastq |= (st < n && ny < 0 ? 1u : 0u) << st;
+        { const int2 pr = __ldcs(prs + min(st + 1, n_last)); nx = pr.x; ny = pr.y; }
+        cp_async_commit();
+    }
+
+    uint64_t acc[RPT][K];
     uint32_t flag = 0;
 #pragma unroll
-    for (int c = 0; c < K; c++) { acc[c] = 0; a_nxt[c] = 0; }
+    for (int rr = 0; rr < RPT; rr++)
 #pragma unroll
-    for (int i = 0; i < Cfg::CPT; i++) b_nxt[i] = make_ulonglong2(0, 0);
+        for (int c = 0; c < K; c++) acc[rr][c] = 0;
 
-    auto prefetch = [&](int64_t pp) {
-        const int2 pr = pairs[pp];
-        const ulonglong2 *ap = reinterpret_cast<const ulonglong2 *>(a_vals + (size_t)pr.x * (K * K) + (size_t)r * K);
-#pragma unroll
-        for (int i = 0; i < K / 2; i++) {
-            const ulonglong2 v = ap[i];
-            a_nxt[2 * i] = v.x;
-            a_nxt[2 * i + 1] = v.y;
-        }
-        const ulonglong2 *bp = reinterpret_cast<const ulonglong2 *>(b_vals + (size_t)pr.y * (K * K));
-#pragma unroll
-        for (int i = 0; i < Cfg::CPT; i++) b_nxt[i] = bp[r + K * i]; // chunk r + K*i: coalesced over the group
-    };
-    if (p < p_end) prefetch(p);
+    // per-thread read addresses inside a stage: two A rows (swizzled chunks) and the B tile
+    const unsigned gbase = wbase + grp * Cfg::GROUP_STRIDE;
+    const unsigned hb16 = K == 8 ? ((h >> 1) & 1) * 16 : 0;
 
-    for (int s = 0; s < steps; s++) {
-        const bool active = p < p_end;
-        unsigned char *buf = wbase + (s & 1) * Cfg::BUF_BYTES;
-        if (active) {
-#pragma unroll
-            for (int c = 0; c < K; c++) a_cur[c] = a_nxt[c];
-#pragma unroll
-            for (int i = 0; i < Cfg::CPT; i++)
-                *reinterpret_cast<ulonglong2 *>(buf + (r + K * i) * 16) = b_nxt[i]; // natural tile layout
+    auto step = [&](int ST, int k) {
+        cp_async_wait<STAGES - 2>(); // this thread's copies for step k have landed
+        __syncwarp();                // ... and everybody else's; everybody is done reading step k-1's stage
+        {
+            const int kk = k + (STAGES - 1);
+            issue((ST + STAGES - 1) % STAGES, nx, ny & 0x7fffffff);
+            lastq |= (kk < n && ny < 0 ? 1u : 0u) << (STAGES - 1);
+            { const int2 pr = __ldcs(prs + min(kk + 1, n_last)); nx = pr.x; ny = pr.y; }
+            cp_async_commit();
         }
-        __syncwarp();
-        if (active) {
-            if (p + 1 < p_end) prefetch(p + 1);
-            const ulonglong2 *bs = reinterpret_cast<const ulonglong2 *>(buf);
+        if (k < n) {
+            const unsigned st = gbase + ST * Cfg::STAGE_BYTES;
+            uint64_t a_cur[RPT][K];
+#pragma unroll
+            for (int rr = 0; rr < RPT; rr++) {
+                const int r = h + TPT * rr;
+                const unsigned row = st + r * (K * 8);
+#pragma unroll
+                for (int i = 0; i < K / 2; i++) {
+                    // chunk i of row r sits at ((i ^ (r >> 1)) & 3) * 16 for k=8 (see a_chunk_offset);
+                    // r >> 1 = (h >> 1) + 2*rr, so the offset is ((i ^ 2rr) * 16) ^ hb16
+                    const unsigned off = K == 8 ? ((unsigned)(((i ^ (2 * rr)) & 3) * 16) ^ hb16) : (unsigned)(i * 16);
+                    const ulonglong2 v = lds128(row + off);
+                    a_cur[rr][2 * i] = v.x;
+                    a_cur[rr][2 * i + 1] = v.y;
+                }
+            }
+            const unsigned bsm = st + Cfg::TILE_BYTES;
 #pragma unroll
             for (int j = 0; j < K; j++) {
 #pragma unroll
                 for (int c2 = 0; c2 < K / 2; c2++) {
-                    const ulonglong2 bv = bs[j * (K / 2) + c2]; // broadcast inside the group
-                    mac_flag(acc[2 * c2], flag, a_cur[j], bv.x);
-                    mac_flag(acc[2 * c2 + 1], flag, a_cur[j], bv.y);
+                    const ulonglong2 bv = lds128(bsm + (j * (K / 2) + c2) * 16); // broadcast inside the group
+#pragma unroll
+                    for (int rr = 0; rr < RPT; rr++) {
+                        mac_flag(acc[rr][2 * c2], flag, a_cur[rr][j], bv.x);
+                        mac_flag(acc[rr][2 * c2 + 1], flag, a_cur[rr][j], bv.y);
+                    }
                 }
             }
-            p++;
-            if (p == pe) { // last pair of the tile: write row r of the tile, move on
+            if (lastq & 1u) { // last pair of the tile: write this thread's rows, move on
                 if (flag == 0xffffffffu) {
-                    refold_row_exact<K>(a_vals, b_vals, pairs, pair_ptr[t], pe, r, acc);
-                    atomicAdd(refold_count, 1ull);
+                    const int64_t p0 = pair_ptr[t], p1 = (prs - pairs) + k + 1;
+#pragma unroll
+                    for (int rr = 0; rr < RPT; rr++) {
+                        uint64_t exact[K]; // only this copy lives in local memory, not the accumulators
+                        refold_row_exact<K>(a_vals, b_vals, pairs, p0, p1, h + TPT * rr, exact);
+#pragma unroll
+                        for (int c = 0; c < K; c++) acc[rr][c] = exact[c];
+                    }
+                    atomicAdd(refold_count, (unsigned long long)RPT);
                 }
-                ulonglong2 *out = reinterpret_cast<ulonglong2 *>(c_vals + (size_t)t * (K * K) + (size_t)r * K);
 #pragma unroll
-                for (int i = 0; i < K / 2; i++) out[i] = make_ulonglong2(acc[2 * i], acc[2 * i + 1]);
+                for (int rr = 0; rr < RPT; rr++) {
+                    ulonglong2 *out = reinterpret_cast<ulonglong2 *>(c_vals + (size_t)t * (K * K) +
+                                                                     (size_t)(h + TPT * rr) * K);
 #pragma unroll
-                for (int c = 0; c < K; c++) acc[c] = 0;
+                    for (int i = 0; i < K / 2; i++)
+                        __stcs(&out[i], make_ulonglong2(acc[rr][2 * i], acc[rr][2 * i + 1]));
+#pragma unroll
+                    for (int c = 0; c < K; c++) acc[rr][c] = 0;
+                }
                 flag = 0;
                 t++;
-                if (t < t_end) pe = pair_ptr[t + 1];
             }
         }
+        lastq >>= 1;
+    };
+
+    for (int k0 = 0; k0 < steps; k0 += STAGES) {
+#pragma unroll
+        for (int st = 0; st < STAGES; st++)
+            if (k0 + st < steps) step(st, k0 + st); // warp-uniform
     }
+    cp_async_wait<0>();
+}
+
+struct NumericTuning { int Q; int panel_mb; int stages; int warps; };
+
+NumericTuning numeric_tuning()
+{
+    NumericTuning tn = {96, 1 << 20, 2, 4}; // panels off by default: measured no gain on cfg2 (see profiles/)
+    if (const char *e = getenv("BSP_NUM_Q")) { int v = atoi(e); if (v >= 1) tn.Q = v; }
+    if (const char *e = getenv("BSP_NUM_PANEL_MB")) { int v = atoi(e); if (v >= 1) tn.panel_mb = v; }
+    if (const char *e = getenv("BSP_NUM_STAGES")) { int v = atoi(e); if (v == 2 || v == 3) tn.stages = v; }
+    if (const char *e = getenv("BSP_NUM_WARPS")) { int v = atoi(e); if (v == 4 || v == 8) tn.warps = v; }
+    return tn;
+}
+
+template <int K, int STAGES, int WARPS>
+int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym, int nbr,
+                    const int32_t *c_rowptr, uint64_t *c_vals, const NumericTuning &tn)
+{
+    using Cfg = RowsCfg<K>;
+    const int groups_per_cta = WARPS * Cfg::GROUPS;
+    // panels: keep the touched part of B well inside L2
+    const int64_t b_bytes = B->nnzb * (int64_t)K * K * 8;
+    int npanels = (int)((b_bytes + (int64_t)tn.panel_mb * (1 << 20) - 1) / ((int64_t)tn.panel_mb * (1 << 20)));
+    if (npanels < 1) npanels = 1;
+    if (npanels > 64) npanels = 64;
+    if (npanels > B->nbc) npanels = B->nbc > 0 ? B->nbc : 1;
+    const int panel_w = (B->nbc + npanels - 1) / npanels;
+    const int Q = tn.Q;
+    const int64_t nseg = (int64_t)nbr * npanels;
+    const int64_t max_chunks64 = sym->nprod / Q + nseg + 1;
+    if (max_chunks64 > 0x7fffff00LL) BSP_FAIL(ctx, BSP_ERR_LIMIT, "numeric pass: too many chunks");
+    const int max_chunks = (int)max_chunks64;
+
+    int32_t *seg_ts = nullptr, *seg_nch = nullptr, *seg_off = nullptr;
+    int2 *chunk_tiles = nullptr;
+    BSP_TRY(bsp_alloc(ctx, &seg_ts, (size_t)nseg + 1));
+    BSP_TRY(bsp_alloc(ctx, &seg_nch, (size_t)nseg + 1));
+    BSP_TRY(bsp_alloc(ctx, &seg_off, (size_t)nseg + 1));
+    BSP_TRY(bsp_alloc(ctx, &chunk_tiles, (size_t)max_chunks));
+    seg_bounds_kernel<<<(unsigned)((nseg + 1 + 255) / 256), 256, 0, ctx->stream>>>(nbr, npanels, panel_w, c_rowptr,
+                                                                                   sym->c_colidx, sym->pair_ptr, Q,
+                                                                                   seg_ts, seg_nch);
+    BSP_LAUNCH_CHECK(ctx);
+    BSP_TRY(bsp_scan_i32(ctx, seg_nch, seg_off, nseg + 1, nullptr));
+    chunk_fill_kernel<<<(unsigned)((max_chunks + 255) / 256), 256, 0, ctx->stream>>>(
+        nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, seg_ts, seg_off, chunk_tiles);
+    BSP_LAUNCH_CHECK(ctx);
+
+    const size_t smem = (size_t)WARPS * STAGES * Cfg::STAGE_BYTES;
+    auto kern = numeric_rows_kernel<K, STAGES, WARPS>;
+    BSP_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int grid = (max_chunks + groups_per_cta - 1) / groups_per_cta;
+    kern<<<grid, WARPS * 32, smem, ctx->stream>>>(A->vals, B->vals, sym->pair_ptr, sym->pairs, chunk_tiles,
+                                                  seg_off + nseg, c_vals, (unsigned long long *)ctx->d_counters);
+    BSP_LAUNCH_CHECK(ctx);
+    bsp_release(ctx, seg_ts); bsp_release(ctx, seg_nch); bsp_release(ctx, seg_off); bsp_release(ctx, chunk_tiles);
+    return BSP_OK;
 }
 
 template <int K>
-int launch_rows(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym, uint64_t *c_vals)
+int launch_rows(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym, int nbr,
+                const int32_t *c_rowptr, uint64_t *c_vals)
 {
-    using Cfg = RowsCfg<K>;
-    const int groups_per_cta = (ROWS_THREADS / 32) * Cfg::GROUPS;
-    // about four waves of chunks, but never chunks smaller than 8 tile products
-    int64_t want_groups = (int64_t)ctx->sm_count * 2 * groups_per_cta * 4;
-    int64_t Q = (sym->nprod + want_groups - 1) / want_groups;
-    if (Q < 8) Q = 8;
-    int64_t nchunks64 = (sym->nprod + Q - 1) / Q;
-    if (nchunks64 < 1) nchunks64 = 1;
-    const int nchunks = (int)nchunks64;
-    int32_t *chunk_tile = nullptr;
-    BSP_TRY(bsp_alloc(ctx, &chunk_tile, (size_t)nchunks + 1));
-    chunk_bounds_kernel<<<(nchunks + 1 + 255) / 256, 256, 0, ctx->stream>>>(sym->pair_ptr, sym->nnzb_c, sym->nprod, Q,
-                                                                            nchunks, chunk_tile);
-    BSP_LAUNCH_CHECK(ctx);
-    const int grid = (nchunks + groups_per_cta - 1) / groups_per_cta;
-    numeric_rows_kernel<K><<<grid, ROWS_THREADS, 0, ctx->stream>>>(A->vals, B->vals, sym->pair_ptr, sym->pairs,
-                                                                   chunk_tile, nchunks, c_vals,
-                                                                   (unsigned long long *)ctx->d_counters);
-    BSP_LAUNCH_CHECK(ctx);
-    bsp_release(ctx, chunk_tile);
-    return BSP_OK;
+    const NumericTuning tn = numeric_tuning();
+    if (tn.stages == 3 && tn.warps == 4) return launch_rows_cfg<K, 3, 4>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
+    if (tn.stages == 2 && tn.warps == 8) return launch_rows_cfg<K, 2, 8>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
+    if (tn.stages == 3 && tn.warps == 8) return launch_rows_cfg<K, 3, 8>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
+    return launch_rows_cfg<K, 2, 4>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
 }
 
 } // namespace
@@ -263,8 +486,8 @@ int bsp_numeric(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
     const int k = A->k;
     if (!ctx->force_generic && (k == 4 || k == 8)) {
         BSP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(unsigned long long), ctx->stream));
-        if (k == 8) BSP_TRY(launch_rows<8>(ctx, A, B, sym, c_vals));
-        else BSP_TRY(launch_rows<4>(ctx, A, B, sym, c_vals));
+        if (k == 8) BSP_TRY(launch_rows<8>(ctx, A, B, sym, A->nbr, sym->c_rowptr, c_vals));
+        else BSP_TRY(launch_rows<4>(ctx, A, B, sym, A->nbr, sym->c_rowptr, c_vals));
         if (path) *path = k;
         if (exact_refolds) {
             unsigned long long *h = (unsigned long long *)((char *)ctx->pinned + 64);

@@ -228,7 +228,11 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         }
         __syncthreads();
     }
-    // 6. stream the row's pairs out
+    // 6. mark the last pair of every tile (sign bit of .y): the numeric pass finds tile ends
+    //    in the pair stream itself instead of chasing pair_ptr
+    for (int t = tid; t < T; t += FILL_THREADS) sp[cur[t] - 1].y |= (int)0x80000000;
+    __syncthreads();
+    // 7. stream the row's pairs out
     for (int x = tid; x < P; x += FILL_THREADS) pairs[pbase + x] = sp[x];
 }
 
@@ -330,7 +334,13 @@ sym_fill_global_kernel(const int32_t *__restrict__ rowlist, const int32_t *__res
         __threadfence_block();
         __syncthreads();
     }
-    // slots now hold tile ends; shift by one inside the row (last chunk first) to get tile starts
+    // slots now hold tile ends: mark the last pair of every tile (sign bit of .y) ...
+    for (int t = tid; t < T; t += FILLG_THREADS) {
+        const unsigned long long e = ((volatile unsigned long long *)pair_ptr)[(size_t)cbase + t];
+        pairs[e - 1].y |= (int)0x80000000;
+    }
+    __syncthreads();
+    // ... then shift by one inside the row (last chunk first) to turn ends into starts
     const int nchunk = (T + FILLG_THREADS - 1) / FILLG_THREADS;
     for (int ch = nchunk - 1; ch >= 0; ch--) {
         const int t = ch * FILLG_THREADS + tid;
