@@ -197,6 +197,96 @@ def reference_arm(args):
 
 
 # --------------------------------------------------------------------------------------------
+# secondary figure: chain milliseconds (BASELINE.json configs[2])
+# --------------------------------------------------------------------------------------------
+CHAIN = dict(n_mats=64, n=16384, k=4, half_band=4, density=0.5, kind="u64")
+
+
+def chain_matrix(i):
+    """Matrix i of the chain workload: banded block pattern (|brow - bcol| <= half_band, each
+    slot kept with probability `density`), so fill-in stays bounded: the product of m factors has
+    half-band m * half_band.  BASELINE.json gives no density for the chain; this is our choice."""
+    import bsp_gen
+    c = CHAIN
+    G = c["n"] // c["k"]
+    br, bc = bsp_gen.banded_pattern(G, c["half_band"], c["density"], 5000 + i)
+    v = bsp_gen.values(5000 + i, br.size * c["k"] * c["k"], c["kind"]).reshape(-1, c["k"], c["k"])
+    return c["n"], c["n"], c["k"], br, bc, v
+
+
+def run_chain(torch, dist, ctx, rank, world, steps, warmup):
+    """Chain of 64 matrices split into contiguous sub-chains over the ranks exactly as the
+    reference splits it over MPI ranks (cu:438-456), local pairwise tree per rank, then the
+    step-doubling merge of the partial products over NCCL send/recv (strong scaling: the
+    chain is fixed).  Returns dict for the JSON line (rank 0) or None."""
+    import bsp_dist
+    import bspgemm
+    parts = bsp_dist.split_chain(CHAIN["n_mats"], world)
+    mine = parts[rank] if rank < len(parts) else None
+    mats = [ctx.matrix_from_coo(*chain_matrix(i)) for i in range(mine[0], mine[1] + 1)] if mine else []
+    nprod = 0
+    sent = 0
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one():
+        nonlocal nprod, sent
+        st = bspgemm.Stats()
+        partial = ctx.helper2(mats, stats=st) if mats else None
+        nprod = st.nprod
+        if world == 1:
+            return partial
+
+        def mul(a, b):
+            nonlocal nprod
+            s2 = bspgemm.Stats()
+            c = ctx.helper(a, b, stats=s2)
+            nprod += s2.nprod
+            return c
+
+        def send(m, dst):
+            nonlocal sent
+            pl = bsp_dist.matrix_to_payload(torch, m)
+            sent += pl.nbytes
+            bsp_dist.send_payload(dist, pl, dst)
+
+        def recv(src):
+            return bsp_dist.payload_to_matrix(torch, ctx, bsp_dist.recv_payload(dist, torch, src, "cuda"))
+        return bsp_dist.tree_merge(rank, len(parts), partial, mul, send, recv)
+
+    res = None
+    for _ in range(warmup):
+        res = one()
+    sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(torch.cuda.current_stream())
+    for _ in range(steps):
+        sent = 0
+        res = one()
+    e1.record(torch.cuda.current_stream())
+    sync()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device="cuda")
+    w = torch.tensor([float(nprod)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(w, op=dist.ReduceOp.SUM)
+    if rank != 0:
+        return None
+    k = CHAIN["k"]
+    return {"ms": t.item(), "unit": "ms", "n_gpus": world, "scaling": "strong",
+            "workload": "chain of %d matrices, n=%d, k=%d, banded pattern (half-band %d blocks, %.0f%% filled), uint64; "
+                        "sub-chains of %d per GPU, NCCL tree merge" % (CHAIN["n_mats"], CHAIN["n"], k, CHAIN["half_band"],
+                                                                      CHAIN["density"] * 100, CHAIN["n_mats"] // max(len(parts), 1)),
+            "products": CHAIN["n_mats"] - 1, "nprod_total": int(w.item()), "result_nnzb": int(res.nnzb),
+            "useful_gflops": 2.0 * k ** 3 * w.item() / (t.item() * 1e-3) / 1e9,
+            "rank0_bytes_sent_per_step": int(sent)}
+
+
+# --------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------
 
@@ -210,6 +300,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 3)")
+    ap.add_argument("--no-chain", action="store_true")
+    ap.add_argument("--chain-steps", type=int, default=2)
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -303,6 +395,11 @@ def main():
                    "api": "bsp_multiply_host (pinned host buffers in, pinned host buffers out)"}
             del ha, hb, ho
 
+        chain = None
+        if not args.no_chain:
+            A.free(); B.free()
+            chain = run_chain(torch, dist, ctx, rank, world, max(1, args.chain_steps), 1)
+
         if rank == 0:
             peak, peak_src = measured_peak()
             alg = algorithmic_bytes(st.nnzb_a, st.nnzb_b, st.nnzb_c, G, k)
@@ -330,6 +427,8 @@ def main():
             }
             if e2e:
                 line["e2e"] = e2e
+            if chain:
+                line["chain"] = chain
             if world == 1 and not args.no_cpu:
                 try:
                     cb = cpu_reference_measure(n, k, d, steps=1, warmup=0)
@@ -337,7 +436,6 @@ def main():
                 except Exception as ex:  # the baseline is reported, never load-bearing
                     line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(ex)}
             print(json.dumps(line))
-        A.free(); B.free()
         ctx.close()
     if world > 1:
         dist.destroy_process_group()

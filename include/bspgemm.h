@@ -91,6 +91,12 @@ int bsp_mat_to_coo(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol,
 int bsp_mat_device_view(const bsp_mat *m, int32_t *nbrows, int32_t *nbcols,
                         const int32_t **d_rowptr, const int32_t **d_colidx, const uint64_t **d_vals);
 
+/* Copy the CSR-of-blocks arrays into caller-owned DEVICE buffers (sizes as in
+ * bsp_mat_device_view): the sending side of the partial-product exchange that replaces
+ * MPI_Send of header / keys / values (cu:471-506); the buffers can be handed to NCCL. */
+int bsp_mat_export_device(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_rowptr, int32_t *d_colidx,
+                          uint64_t *d_vals);
+
 /* Build a matrix from a device CSR-of-blocks view (arrays are copied).  The receiving side
  * of the partial-product exchange that replaces MPI_Recv + map rebuild (cu:513-551). */
 int bsp_mat_from_device_bcsr(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows,
@@ -127,8 +133,8 @@ int bsp_prune_zero(bsp_ctx *ctx, bsp_mat *m);
 
 /* One call from host buffers to host buffers: upload A and B, multiply, download C sorted.
  * The shape of the reference's helper seen from its caller (one_matrix in, one_matrix out).
- * Pass NULL output arrays to only obtain *nnzb_c (then call again), or call
- * bsp_multiply_host_alloc. cap_c = capacity of the output arrays in tiles. */
+ * Pass NULL output arrays to only obtain *nnzb_c (then call again with buffers).
+ * cap_c = capacity of the output arrays in tiles. */
 int bsp_multiply_host(bsp_ctx *ctx, int32_t k,
                       int32_t rows_a, int32_t cols_a, int64_t nnzb_a, const int32_t *brow_a,
                       const int32_t *bcol_a, const uint64_t *vals_a,

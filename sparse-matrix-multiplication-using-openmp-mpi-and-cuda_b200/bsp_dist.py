@@ -92,3 +92,81 @@ def chain_ranks_on_one_context(ctx, mats, P, stats_list=None):
     for s, e in split_chain(len(mats), P):
         parts.append(ctx.helper2(mats[s:e + 1]))
     return ctx.helper2(parts) if len(parts) > 1 else parts[0]
+
+
+# ---- partial-product exchange over torch.distributed (NCCL on GPUs, gloo in the CPU tests) ----
+# Wire format of one matrix (replaces the reference's header / keys / values messages,
+# cu:471-506): int64 header [rows, cols, k, nbrows, nbcols, nnzb], then rowptr int32[nbrows+1],
+# colidx int32[nnzb], vals int64[nnzb*k*k] (uint64 bit patterns).
+
+HEADER_LEN = 6
+
+
+class Payload:
+    """A matrix as four tensors on one device (CPU for gloo, CUDA for NCCL)."""
+
+    def __init__(self, header, rowptr, colidx, vals):
+        self.header, self.rowptr, self.colidx, self.vals = header, rowptr, colidx, vals
+
+    @property
+    def nbytes(self):
+        return sum(t.numel() * t.element_size() for t in (self.header, self.rowptr, self.colidx, self.vals))
+
+
+def send_payload(dist, pl, dst):
+    dist.send(pl.header, dst)
+    dist.send(pl.rowptr, dst)
+    if pl.colidx.numel():
+        dist.send(pl.colidx, dst)
+        dist.send(pl.vals, dst)
+
+
+def recv_payload(dist, torch, src, device):
+    header = torch.empty(HEADER_LEN, dtype=torch.int64, device=device)
+    dist.recv(header, src)
+    rows, cols, k, nbr, nbc, nnzb = [int(x) for x in header.cpu().tolist()]
+    rowptr = torch.empty(nbr + 1, dtype=torch.int32, device=device)
+    dist.recv(rowptr, src)
+    colidx = torch.empty(nnzb, dtype=torch.int32, device=device)
+    vals = torch.empty(nnzb * k * k, dtype=torch.int64, device=device)
+    if nnzb:
+        dist.recv(colidx, src)
+        dist.recv(vals, src)
+    return Payload(header, rowptr, colidx, vals)
+
+
+def matrix_to_payload(torch, mat):
+    """Device matrix (bspgemm.Matrix) -> Payload of CUDA tensors (device-to-device copies)."""
+    rows, cols, k, nnzb = mat.info()
+    nbr, nbc, _, _, _ = mat.device_view()
+    header = torch.tensor([rows, cols, k, nbr, nbc, nnzb], dtype=torch.int64, device="cuda")
+    rowptr = torch.empty(nbr + 1, dtype=torch.int32, device="cuda")
+    colidx = torch.empty(max(nnzb, 1), dtype=torch.int32, device="cuda")
+    vals = torch.empty(max(nnzb * k * k, 1), dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    mat.export_device(rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr())
+    return Payload(header, rowptr, colidx[:nnzb], vals[:nnzb * k * k])
+
+
+def payload_to_matrix(torch, ctx, pl):
+    rows, cols, k, nbr, nbc, nnzb = [int(x) for x in pl.header.cpu().tolist()]
+    torch.cuda.synchronize()
+    return ctx.matrix_from_device_bcsr(rows, cols, k, nbr, nbc, nnzb, pl.rowptr.data_ptr(),
+                                       pl.colidx.data_ptr() if nnzb else 0, pl.vals.data_ptr() if nnzb else 0)
+
+
+def tree_merge(rank, nparts, partial, multiply, send, recv):
+    """Step-doubling merge of `nparts` partial products held by ranks 0..nparts-1 (one each).
+    multiply(left, right) -> product; send(obj, dst); recv(src) -> obj.  Returns the final
+    product on rank 0 and None elsewhere.  Same association as helper2 over the partials
+    (cu:569-571), see association_by_schedule."""
+    held = partial
+    for step in merge_schedule(nparts):
+        for receiver, sender in step:
+            if rank == sender:
+                send(held, receiver)
+                held = None
+            elif rank == receiver:
+                other = recv(sender)
+                held = multiply(held, other)
+    return held if rank == 0 else None

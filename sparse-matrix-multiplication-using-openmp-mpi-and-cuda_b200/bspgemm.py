@@ -52,6 +52,7 @@ _SIGNATURES = {
     "bsp_mat_info": (C.c_int, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "bsp_mat_to_coo": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "bsp_mat_device_view": (C.c_int, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP)]),
+    "bsp_mat_export_device": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "bsp_mat_from_device_bcsr": (C.c_int, [_VP, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP, C.POINTER(_VP)]),
     "bsp_mat_free": (None, [_VP, _VP]),
     "bsp_spgemm": (C.c_int, [_VP, _VP, _VP, C.POINTER(_VP), C.POINTER(Stats)]),
@@ -142,6 +143,10 @@ class Matrix:
         self.ctx._ck(self.ctx.lib.bsp_mat_device_view(self.handle, C.byref(nr), C.byref(nc), C.byref(p1), C.byref(p2),
                                                       C.byref(p3)))
         return nr.value, nc.value, p1.value or 0, p2.value or 0, p3.value or 0
+
+    def export_device(self, d_rowptr, d_colidx, d_vals):
+        """Copy rowptr / colidx / vals into caller-owned device buffers (raw addresses)."""
+        self.ctx._ck(self.ctx.lib.bsp_mat_export_device(self.ctx.handle, self.handle, d_rowptr, d_colidx, d_vals))
 
     def prune_zero(self):
         self.ctx._ck(self.ctx.lib.bsp_prune_zero(self.ctx.handle, self.handle))

@@ -46,6 +46,7 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     BSP_TRY(new_empty_like(ctx, A->rows, B->cols, A->k, A->nbr, B->nbc, &c)); // cu:280-282
     *C = c;
     BSP_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+    bsp_trace_mark(ctx, "start");
     bsp_symbolic_out sym;
     BSP_TRY(bsp_symbolic(ctx, A, B, row_lo, row_hi, &sym));
     BSP_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
@@ -53,7 +54,9 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     c->colidx = sym.c_colidx;
     c->nnzb = sym.nnzb_c;
     BSP_TRY(bsp_alloc(ctx, &c->vals, (size_t)sym.nnzb_c * A->k * A->k));
+    bsp_trace_mark(ctx, "alloc_c");
     BSP_TRY(bsp_numeric(ctx, A, B, &sym, c->vals, &st.exact_refolds, &st.numeric_path));
+    bsp_trace_mark(ctx, "numeric");
     BSP_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
     bsp_release(ctx, sym.pair_ptr);
     bsp_release(ctx, sym.pairs);
@@ -65,6 +68,7 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     st.nnzb_c = sym.nnzb_c; st.nprod = sym.nprod;
     st.ms_symbolic = ms01; st.ms_numeric = ms12; st.ms_total = ms01 + ms12;
     st.launches = ctx->launches - launches0;
+    bsp_trace_dump(ctx);
     if (stats) *stats = st;
     return BSP_OK;
 }
@@ -131,6 +135,8 @@ int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
     {
         const char *fg = getenv("BSP_FORCE_GENERIC");
         ctx->force_generic = fg && fg[0] == '1';
+        const char *tr = getenv("BSP_TRACE");
+        ctx->trace = tr && tr[0] == '1';
     }
     // keep freed blocks in the stream-ordered pool: a chain allocates and frees every product
     cudaMemPool_t pool;
@@ -146,6 +152,8 @@ void bsp_ctx_destroy(bsp_ctx *ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < 4; i++)
         if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    for (int i = 0; i < 32; i++)
+        if (ctx->trace_ev[i]) cudaEventDestroy(ctx->trace_ev[i]);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->d_counters) cudaFree(ctx->d_counters);
     if (ctx->owns_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -257,6 +265,21 @@ int bsp_mat_device_view(const bsp_mat *m, int32_t *nbrows, int32_t *nbcols, cons
     if (d_rowptr) *d_rowptr = m->rowptr;
     if (d_colidx) *d_colidx = m->colidx;
     if (d_vals) *d_vals = m->vals;
+    return BSP_OK;
+}
+
+int bsp_mat_export_device(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_rowptr, int32_t *d_colidx, uint64_t *d_vals)
+{
+    if (!ctx || !valid_mat(m)) return BSP_ERR_ARG;
+    BSP_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t kk = (size_t)m->k * m->k;
+    if (d_rowptr)
+        BSP_CUDA(ctx, cudaMemcpyAsync(d_rowptr, m->rowptr, ((size_t)m->nbr + 1) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (d_colidx && m->nnzb)
+        BSP_CUDA(ctx, cudaMemcpyAsync(d_colidx, m->colidx, (size_t)m->nnzb * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (d_vals && m->nnzb)
+        BSP_CUDA(ctx, cudaMemcpyAsync(d_vals, m->vals, (size_t)m->nnzb * kk * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return BSP_OK;
 }
 

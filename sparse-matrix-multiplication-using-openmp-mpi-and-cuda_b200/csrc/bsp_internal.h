@@ -27,6 +27,10 @@ struct bsp_ctx {
     size_t pinned_bytes;
     void *d_counters;    // 256 B of device counters (exact-refold count of the numeric pass)
     bool force_generic;  // BSP_FORCE_GENERIC=1: always use the any-k exact numeric kernel (tests)
+    bool trace;          // BSP_TRACE=1: per-sub-phase device timings of every product on stderr
+    int ntrace;
+    cudaEvent_t trace_ev[32];
+    const char *trace_label[32];
     char err[512];
 };
 
@@ -80,6 +84,28 @@ static inline int bsp_alloc(bsp_ctx *ctx, T **p, size_t count)
 static inline void bsp_release(bsp_ctx *ctx, void *p)
 {
     if (p) cudaFreeAsync(p, ctx->stream);
+}
+
+// BSP_TRACE=1: mark a point on the stream; bsp_trace_dump prints the gaps between marks
+static inline void bsp_trace_mark(bsp_ctx *ctx, const char *label)
+{
+    if (!ctx->trace || ctx->ntrace >= 32) return;
+    if (!ctx->trace_ev[ctx->ntrace]) cudaEventCreate(&ctx->trace_ev[ctx->ntrace]);
+    cudaEventRecord(ctx->trace_ev[ctx->ntrace], ctx->stream);
+    ctx->trace_label[ctx->ntrace++] = label;
+}
+static inline void bsp_trace_dump(bsp_ctx *ctx)
+{
+    if (!ctx->trace || ctx->ntrace < 2) { ctx->ntrace = 0; return; }
+    cudaEventSynchronize(ctx->trace_ev[ctx->ntrace - 1]);
+    fprintf(stderr, "[bsp trace]");
+    for (int i = 1; i < ctx->ntrace; i++) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ctx->trace_ev[i - 1], ctx->trace_ev[i]);
+        fprintf(stderr, " %s=%.3f", ctx->trace_label[i], ms);
+    }
+    fprintf(stderr, "\n");
+    ctx->ntrace = 0;
 }
 
 #define BSP_LAUNCH_CHECK(ctx)                  \

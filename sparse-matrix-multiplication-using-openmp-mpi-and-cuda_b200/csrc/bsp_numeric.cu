@@ -453,6 +453,7 @@ int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_
         nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, seg_ts, seg_off, chunk_tiles);
     BSP_LAUNCH_CHECK(ctx);
 
+    bsp_trace_mark(ctx, "num_schedule");
     const size_t smem = (size_t)WARPS * STAGES * Cfg::STAGE_BYTES;
     auto kern = numeric_rows_kernel<K, STAGES, WARPS>;
     BSP_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -134,42 +134,71 @@ __device__ __forceinline__ int block_excl_scan_i32(int v, int *sm33, int *total)
     return res;
 }
 
+// Shared-memory budget of one row: 8*words (bitmap + rank table) + 8*(acap+1) (A entries)
+// + 4*(pcap+4) (tile counters) + 2*pcap (tile of every product) + 8*pcap (the row's pairs).
+__host__ __device__ inline size_t fill_smem_bytes(int words, int pcap, int acap)
+{
+    return 8 * (size_t)words + 8 * ((size_t)acap + 2) + 4 * ((size_t)pcap + 4) + 2 * ((size_t)pcap + 8) + 8 * (size_t)pcap;
+}
+
 __global__ void __launch_bounds__(FILL_THREADS)
 sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
                      const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
-                     const int32_t *__restrict__ b_colidx, int words, int pcap,
+                     const int32_t *__restrict__ b_colidx, int words, int pcap, int acap,
                      const int32_t *__restrict__ c_rowptr, const int64_t *__restrict__ row_prod_ptr,
                      int32_t *__restrict__ c_colidx, int64_t *__restrict__ pair_ptr, int2 *__restrict__ pairs)
 {
-    extern __shared__ uint32_t smem[];
+    extern __shared__ __align__(16) uint32_t smem[];
     __shared__ int sm33[33];
     uint32_t *bm = smem;
     uint32_t *wrank = bm + words;
-    int *cur = (int *)(wrank + words);                          // [pcap + 2] per-tile counter, then cursor
-    int2 *sp = (int2 *)(cur + ((pcap + 2 + 1) & ~1));           // [pcap] the row's pairs
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = FILL_THREADS / 32;
+    int2 *aent = (int2 *)(wrank + words);                        // [acap+2] (first B tile, product offset) per A entry
+    int *cur = (int *)(aent + acap + 2);                         // [pcap+4] per-tile counter, then cursor
+    int2 *sp = (int2 *)(cur + pcap + 4);                         // [pcap]   the row's pairs
+    unsigned short *prodt = (unsigned short *)(sp + pcap);       // [pcap+8] output tile (rank in the row) of every product
+    const int tid = threadIdx.x;
     const int row = rowlist[blockIdx.x];
     const int cbase = c_rowptr[row], T = c_rowptr[row + 1] - cbase;
     const int64_t pbase = row_prod_ptr[row];
     const int P = (int)(row_prod_ptr[row + 1] - pbase);
-    const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
+    const int a0 = a_rowptr[row], nA = a_rowptr[row + 1] - a0;
 
     for (int w = tid; w < words; w += FILL_THREADS) bm[w] = 0u;
     for (int t = tid; t < T + 1; t += FILL_THREADS) cur[t] = 0;
-    __syncthreads();
-    // 1. bitmap of reachable block columns (warps over A entries, lanes over B row j)
-    for (int p = a0 + warp; p < a1; p += nwarp) {
-        const int j = a_colidx[p];
-        if (j >= b_nbr) continue;
-        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
-        for (int q = b0 + lane; q < b1; q += 32) {
-            const int c = b_colidx[q];
-            atomicOr(&bm[c >> 5], 1u << (c & 31));
+    // 0. A entries: first tile of B row j and (after the scan) the offset of its products
+    int carry = 0;
+    for (int e0 = 0; e0 < nA; e0 += FILL_THREADS) {
+        const int e = e0 + tid;
+        int b0 = 0, len = 0;
+        if (e < nA) {
+            const int j = a_colidx[a0 + e];
+            if (j < b_nbr) { b0 = b_rowptr[j]; len = b_rowptr[j + 1] - b0; }
         }
+        int tot;
+        const int ex = block_excl_scan_i32(len, sm33, &tot);
+        if (e < nA) aent[e] = make_int2(b0, carry + ex);
+        carry += tot;
+    }
+    if (tid == 0) aent[nA] = make_int2(0, P);
+    __syncthreads();
+    // 1. one pass over the row's products, flattened over the CTA (x = product number): find
+    //    its A entry by binary search in the offset table, read its block column from B once,
+    //    keep it in shared memory (in the area the pairs will occupy later) and set its bit
+    int *tmpc = (int *)sp;
+#pragma unroll 4
+    for (int x = tid; x < P; x += FILL_THREADS) {
+        int lo = 0, hi = nA; // last entry with offset <= x
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (aent[mid].y <= x) lo = mid; else hi = mid;
+        }
+        const int c = b_colidx[aent[lo].x + (x - aent[lo].y)];
+        tmpc[x] = c;
+        atomicOr(&bm[c >> 5], 1u << (c & 31));
     }
     __syncthreads();
     // 2. rank table + sorted colidx of the C row
-    int carry = 0;
+    carry = 0;
     for (int w0 = 0; w0 < words; w0 += FILL_THREADS) {
         const int w = w0 + tid;
         const uint32_t bits = w < words ? bm[w] : 0u;
@@ -188,16 +217,12 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         carry += tot;
     }
     __syncthreads();
-    // 3. pairs per output tile
-    for (int p = a0 + warp; p < a1; p += nwarp) {
-        const int j = a_colidx[p];
-        if (j >= b_nbr) continue;
-        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
-        for (int q = b0 + lane; q < b1; q += 32) {
-            const int c = b_colidx[q];
-            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
-            atomicAdd(&cur[t], 1);
-        }
+    // 3. output tile of every product (16-bit rank in the row) + pairs per tile
+    for (int x = tid; x < P; x += FILL_THREADS) {
+        const int c = tmpc[x];
+        const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+        prodt[x] = (unsigned short)t;
+        atomicAdd(&cur[t], 1);
     }
     __syncthreads();
     // 4. exclusive scan -> first slot of every tile; publish pair_ptr; cur[] becomes the cursor
@@ -214,17 +239,18 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         carry += tot;
     }
     __syncthreads();
-    // 5. ordered placement: A row in ascending j, the CTA over B row j
-    for (int p = a0; p < a1; p++) {
-        const int j = a_colidx[p];
-        if (j >= b_nbr) continue; // uniform
-        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
-        for (int q = b0 + tid; q < b1; q += FILL_THREADS) {
-            const int c = b_colidx[q];
-            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+    // 5. ordered placement: A row in ascending j, the CTA over B row j.  Everything the loop
+    //    touches is in shared memory; inside one j all target tiles differ, so the cursor bump
+    //    needs no atomic, and the barrier between two j keeps the append order.
+    for (int e = 0; e < nA; e++) {
+        const int2 ae = aent[e];
+        const int len = aent[e + 1].y - ae.y;
+        if (len == 0) continue; // uniform
+        for (int i = tid; i < len; i += FILL_THREADS) {
+            const int t = prodt[ae.y + i];
             const int pos = cur[t];
             cur[t] = pos + 1;
-            sp[pos] = make_int2(p, q);
+            sp[pos] = make_int2(a0 + e, ae.x + i);
         }
         __syncthreads();
     }
@@ -359,14 +385,16 @@ sym_fill_global_kernel(const int32_t *__restrict__ rowlist, const int32_t *__res
 // products fits class c when P <= caps[c]; larger than every cap -> class NCLASS-1 (global).
 constexpr int NCLASS = 4;
 
-__global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ row_cnt, const int32_t *__restrict__ row_prod,
-                                     int cap0, int cap1, int cap2, int32_t *__restrict__ lists,
+__global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowptr,
+                                     const int32_t *__restrict__ row_cnt, const int32_t *__restrict__ row_prod,
+                                     int cap0, int cap1, int cap2, int acap, int32_t *__restrict__ lists,
                                      int32_t *__restrict__ counts)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nbr || row_cnt[row] == 0) return;
     const int P = row_prod[row];
-    const int cls = P <= cap0 ? 0 : (P <= cap1 ? 1 : (P <= cap2 ? 2 : 3));
+    int cls = P <= cap0 ? 0 : (P <= cap1 ? 1 : (P <= cap2 ? 2 : 3));
+    if (a_rowptr[row + 1] - a_rowptr[row] > acap) cls = 3; // A row too long for the shared-memory entry table
     const int slot = atomicAdd(&counts[cls], 1);
     lists[(size_t)cls * nbr + slot] = row;
 }
@@ -403,25 +431,29 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     if (grid > max_grid) grid = max_grid;
     if (grid < 1) grid = 1;
     // capacity classes of the shared-memory fill: tile products per row that fit next to the bitmaps
-    //   bytes(pcap) = 8*words + 4*(pcap+3) + 8*pcap
-    auto fill_bytes = [&](int pcap) { return bitmap_bytes + 4 * ((size_t)pcap + 4) + 8 * (size_t)pcap; };
-    int caps[3] = {1536, 8192, 16384};
+        const int acap = 1024;
+    auto fill_bytes = [&](int pcap) { return fill_smem_bytes(words, pcap, acap); };
+    int caps[3] = {1536, 6800, 15000}; // ~3.5 / 2 / 1 CTAs per SM
     if (const char *e = getenv("BSP_SYM_CAPS")) { // test hook: force rows into the larger classes
         int a, b, c;
         if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && a <= b && b <= c) { caps[0] = a; caps[1] = b; caps[2] = c; }
     }
-    for (int c = 0; c < 3; c++)
-        while (caps[c] > 0 && fill_bytes(caps[c]) > 220 * 1024) caps[c] /= 2;
+    for (int c = 0; c < 3; c++) {
+        if (caps[c] > 60000) caps[c] = 60000; // tile ranks are kept as 16-bit values in shared memory
+        while (caps[c] > 2 && fill_bytes(caps[c]) > 220 * 1024) caps[c] /= 2;
+        caps[c] &= ~1;                         // keeps the int2 arrays 8-byte aligned
+    }
     if (nbr > 0) {
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)smem_count));
         sym_count_kernel<<<grid, SYM_THREADS, smem_count, ctx->stream>>>(
             nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, row_lo, row_hi, row_cnt, row_prod);
         BSP_LAUNCH_CHECK(ctx);
-        classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, row_cnt, row_prod, caps[0], caps[1],
-                                                                        caps[2], lists, counts);
+        classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, A->rowptr, row_cnt, row_prod, caps[0],
+                                                                        caps[1], caps[2], acap, lists, counts);
         BSP_LAUNCH_CHECK(ctx);
     }
+    bsp_trace_mark(ctx, "sym_count");
     BSP_TRY(bsp_scan_i32(ctx, row_cnt, out->c_rowptr, (int64_t)nbr + 1, nullptr));
     BSP_TRY(bsp_scan_i32_to_i64(ctx, row_prod, row_prod_ptr, (int64_t)nbr + 1));
 
@@ -432,6 +464,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     BSP_CUDA(ctx, cudaMemcpyAsync(h_nnzb, out->c_rowptr + nbr, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
     BSP_CUDA(ctx, cudaMemcpyAsync(h_nprod, row_prod_ptr + nbr, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
     BSP_CUDA(ctx, cudaMemcpyAsync(h_counts, counts, NCLASS * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    bsp_trace_mark(ctx, "sym_scans");
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     out->nnzb_c = *h_nnzb;
     out->nprod = *h_nprod;
@@ -445,13 +478,14 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     // every row writes its own slots; the closing entry pair_ptr[nnzb_c] = nprod comes from the row scan
     BSP_CUDA(ctx, cudaMemcpyAsync(out->pair_ptr + out->nnzb_c, row_prod_ptr + nbr, sizeof(int64_t),
                                   cudaMemcpyDeviceToDevice, ctx->stream));
+    bsp_trace_mark(ctx, "sym_sync_alloc");
     for (int c = 0; c < 3; c++) {
         if (ncls[c] == 0) continue;
         const size_t bytes = fill_bytes(caps[c]);
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
         sym_fill_smem_kernel<<<ncls[c], FILL_THREADS, bytes, ctx->stream>>>(
-            lists + (size_t)c * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, caps[c], out->c_rowptr,
-            row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
+            lists + (size_t)c * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, caps[c], acap,
+            out->c_rowptr, row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
     if (ncls[3] > 0) {
@@ -462,6 +496,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
             row_prod_ptr, out->c_colidx, (unsigned long long *)out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
+    bsp_trace_mark(ctx, "sym_fill");
     bsp_release(ctx, row_cnt);
     bsp_release(ctx, row_prod);
     bsp_release(ctx, row_prod_ptr);
