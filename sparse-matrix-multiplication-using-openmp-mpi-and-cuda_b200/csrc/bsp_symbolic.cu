@@ -103,7 +103,8 @@ sym_count_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t 
 // placed in ascending j by walking the A row entry by entry with the whole CTA spread over
 // B row j (inside one j every target tile is distinct, so the cursor bump needs no atomic),
 // then streamed to global memory with coalesced stores -- DRAM sees each pair exactly once.
-constexpr int FILL_THREADS = 256;
+constexpr int FILL_THREADS = 512;
+constexpr int FILL_SORT_MAX = 16; // rows whose tiles all have <= this many pairs: parallel placement + tiny sorts
 
 __device__ __forceinline__ int block_excl_scan_i32(int v, int *sm33, int *total)
 {
@@ -134,17 +135,17 @@ __device__ __forceinline__ int block_excl_scan_i32(int v, int *sm33, int *total)
     return res;
 }
 
-// Shared-memory budget of one row: 8*words (bitmap + rank table) + 8*(acap+1) (A entries)
-// + 4*(pcap+4) (tile counters) + 2*pcap (tile of every product) + 8*pcap (the row's pairs).
-__host__ __device__ inline size_t fill_smem_bytes(int words, int pcap, int acap)
+// Shared-memory budget of one row: 8*words (bitmap + rank table) + 8*(acap+2) (A entries)
+// + 4*(tcap+4) (tile counters) + 8*pcap (the row's pairs) + 2*(pcap+8) (tile of every product).
+__host__ __device__ inline size_t fill_smem_bytes(int words, int pcap, int tcap, int acap)
 {
-    return 8 * (size_t)words + 8 * ((size_t)acap + 2) + 4 * ((size_t)pcap + 4) + 2 * ((size_t)pcap + 8) + 8 * (size_t)pcap;
+    return 8 * (size_t)words + 8 * ((size_t)acap + 2) + 4 * ((size_t)tcap + 4) + 8 * (size_t)pcap + 2 * ((size_t)pcap + 8);
 }
 
 __global__ void __launch_bounds__(FILL_THREADS)
 sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
                      const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
-                     const int32_t *__restrict__ b_colidx, int words, int pcap, int acap,
+                     const int32_t *__restrict__ b_colidx, int words, int pcap, int tcap, int acap,
                      const int32_t *__restrict__ c_rowptr, const int64_t *__restrict__ row_prod_ptr,
                      int32_t *__restrict__ c_colidx, int64_t *__restrict__ pair_ptr, int2 *__restrict__ pairs)
 {
@@ -153,8 +154,8 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     uint32_t *bm = smem;
     uint32_t *wrank = bm + words;
     int2 *aent = (int2 *)(wrank + words);                        // [acap+2] (first B tile, product offset) per A entry
-    int *cur = (int *)(aent + acap + 2);                         // [pcap+4] per-tile counter, then cursor
-    int2 *sp = (int2 *)(cur + pcap + 4);                         // [pcap]   the row's pairs
+    int *cur = (int *)(aent + acap + 2);                         // [tcap+4] per-tile counter, then cursor
+    int2 *sp = (int2 *)(cur + tcap + 4);                         // [pcap]   the row's pairs
     unsigned short *prodt = (unsigned short *)(sp + pcap);       // [pcap+8] output tile (rank in the row) of every product
     const int tid = threadIdx.x;
     const int row = rowlist[blockIdx.x];
@@ -227,9 +228,11 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     __syncthreads();
     // 4. exclusive scan -> first slot of every tile; publish pair_ptr; cur[] becomes the cursor
     carry = 0;
+    int maxcnt = 0;
     for (int t0 = 0; t0 < T; t0 += FILL_THREADS) {
         const int t = t0 + tid;
         const int v = t < T ? cur[t] : 0;
+        maxcnt = max(maxcnt, v);
         int tot;
         const int ex = block_excl_scan_i32(v, sm33, &tot);
         if (t < T) {
@@ -238,21 +241,48 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         }
         carry += tot;
     }
-    __syncthreads();
-    // 5. ordered placement: A row in ascending j, the CTA over B row j.  Everything the loop
-    //    touches is in shared memory; inside one j all target tiles differ, so the cursor bump
-    //    needs no atomic, and the barrier between two j keeps the append order.
-    for (int e = 0; e < nA; e++) {
-        const int2 ae = aent[e];
-        const int len = aent[e + 1].y - ae.y;
-        if (len == 0) continue; // uniform
-        for (int i = tid; i < len; i += FILL_THREADS) {
-            const int t = prodt[ae.y + i];
-            const int pos = cur[t];
-            cur[t] = pos + 1;
-            sp[pos] = make_int2(a0 + e, ae.x + i);
+    maxcnt = __syncthreads_or(maxcnt > FILL_SORT_MAX);
+    if (!maxcnt) {
+        // 5a. every tile has few pairs: place all products at once (cursor bumped atomically, any
+        //     order), then put each tile's pairs in ascending A index -- which is ascending j,
+        //     because the A row is sorted -- with a tiny insertion sort, one thread per tile.
+#pragma unroll 2
+        for (int x = tid; x < P; x += FILL_THREADS) {
+            int lo = 0, hi = nA;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (aent[mid].y <= x) lo = mid; else hi = mid;
+            }
+            const int pos = atomicAdd(&cur[prodt[x]], 1);
+            sp[pos] = make_int2(a0 + lo, aent[lo].x + (x - aent[lo].y));
         }
         __syncthreads();
+        for (int t = tid; t < T; t += FILL_THREADS) {
+            const int e1 = cur[t], s1 = t ? cur[t - 1] : 0; // cursors now hold tile ends
+            for (int i = s1 + 1; i < e1; i++) {
+                const int2 v = sp[i];
+                int j = i - 1;
+                while (j >= s1 && sp[j].x > v.x) { sp[j + 1] = sp[j]; j--; }
+                sp[j + 1] = v;
+            }
+        }
+        __syncthreads();
+    } else {
+        // 5b. ordered placement: A row in ascending j, the CTA over B row j.  Everything the loop
+        //     touches is in shared memory; inside one j all target tiles differ, so the cursor bump
+        //     needs no atomic, and the barrier between two j keeps the append order.
+        for (int e = 0; e < nA; e++) {
+            const int2 ae = aent[e];
+            const int len = aent[e + 1].y - ae.y;
+            if (len == 0) continue; // uniform
+            for (int i = tid; i < len; i += FILL_THREADS) {
+                const int t = prodt[ae.y + i];
+                const int pos = cur[t];
+                cur[t] = pos + 1;
+                sp[pos] = make_int2(a0 + e, ae.x + i);
+            }
+            __syncthreads();
+        }
     }
     // 6. mark the last pair of every tile (sign bit of .y): the numeric pass finds tile ends
     //    in the pair stream itself instead of chasing pair_ptr
@@ -387,13 +417,13 @@ constexpr int NCLASS = 4;
 
 __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowptr,
                                      const int32_t *__restrict__ row_cnt, const int32_t *__restrict__ row_prod,
-                                     int cap0, int cap1, int cap2, int acap, int32_t *__restrict__ lists,
-                                     int32_t *__restrict__ counts)
+                                     int cap0, int cap1, int cap2, int tcap0, int tcap1, int tcap2, int acap,
+                                     int32_t *__restrict__ lists, int32_t *__restrict__ counts)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nbr || row_cnt[row] == 0) return;
-    const int P = row_prod[row];
-    int cls = P <= cap0 ? 0 : (P <= cap1 ? 1 : (P <= cap2 ? 2 : 3));
+    const int P = row_prod[row], T = row_cnt[row];
+    int cls = (P <= cap0 && T <= tcap0) ? 0 : ((P <= cap1 && T <= tcap1) ? 1 : ((P <= cap2 && T <= tcap2) ? 2 : 3));
     if (a_rowptr[row + 1] - a_rowptr[row] > acap) cls = 3; // A row too long for the shared-memory entry table
     const int slot = atomicAdd(&counts[cls], 1);
     lists[(size_t)cls * nbr + slot] = row;
@@ -431,17 +461,24 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     if (grid > max_grid) grid = max_grid;
     if (grid < 1) grid = 1;
     // capacity classes of the shared-memory fill: tile products per row that fit next to the bitmaps
-        const int acap = 1024;
-    auto fill_bytes = [&](int pcap) { return fill_smem_bytes(words, pcap, acap); };
-    int caps[3] = {1536, 6800, 15000}; // ~3.5 / 2 / 1 CTAs per SM
+        // capacity classes of the shared-memory fill (tile products / output tiles of a row):
+    // about 8 / 2 / 1 CTAs per SM; larger rows use the global-memory variant
+    const int acap = 512;
+    int caps[3] = {1536, 8200, 15000}, tcaps[3] = {1536, 6000, 15000};
     if (const char *e = getenv("BSP_SYM_CAPS")) { // test hook: force rows into the larger classes
         int a, b, c;
-        if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && a <= b && b <= c) { caps[0] = a; caps[1] = b; caps[2] = c; }
+        if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && a <= b && b <= c) {
+            caps[0] = tcaps[0] = a; caps[1] = tcaps[1] = b; caps[2] = tcaps[2] = c;
+        }
     }
     for (int c = 0; c < 3; c++) {
         if (caps[c] > 60000) caps[c] = 60000; // tile ranks are kept as 16-bit values in shared memory
-        while (caps[c] > 2 && fill_bytes(caps[c]) > 220 * 1024) caps[c] /= 2;
-        caps[c] &= ~1;                         // keeps the int2 arrays 8-byte aligned
+        if (tcaps[c] > caps[c]) tcaps[c] = caps[c];
+        while (caps[c] > 2 && fill_smem_bytes(words, caps[c], tcaps[c], acap) > 220 * 1024) {
+            caps[c] /= 2;
+            if (tcaps[c] > caps[c]) tcaps[c] = caps[c];
+        }
+        caps[c] &= ~1; tcaps[c] &= ~1; // keeps the int2 arrays 8-byte aligned
     }
     if (nbr > 0) {
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -450,7 +487,8 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
             nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, row_lo, row_hi, row_cnt, row_prod);
         BSP_LAUNCH_CHECK(ctx);
         classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, A->rowptr, row_cnt, row_prod, caps[0],
-                                                                        caps[1], caps[2], acap, lists, counts);
+                                                                        caps[1], caps[2], tcaps[0], tcaps[1], tcaps[2],
+                                                                        acap, lists, counts);
         BSP_LAUNCH_CHECK(ctx);
     }
     bsp_trace_mark(ctx, "sym_count");
@@ -481,10 +519,10 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     bsp_trace_mark(ctx, "sym_sync_alloc");
     for (int c = 0; c < 3; c++) {
         if (ncls[c] == 0) continue;
-        const size_t bytes = fill_bytes(caps[c]);
+        const size_t bytes = fill_smem_bytes(words, caps[c], tcaps[c], acap);
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
         sym_fill_smem_kernel<<<ncls[c], FILL_THREADS, bytes, ctx->stream>>>(
-            lists + (size_t)c * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, caps[c], acap,
+            lists + (size_t)c * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, caps[c], tcaps[c], acap,
             out->c_rowptr, row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
