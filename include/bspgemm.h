@@ -118,6 +118,11 @@ int bsp_spgemm(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, bsp_mat **C, bs
 int bsp_spgemm_panel(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo, int32_t row_hi,
                      bsp_mat **C, bsp_stats *stats);
 
+/* Concatenate n block-row panels (results of bsp_spgemm_panel over consecutive, disjoint
+ * row ranges of the same product, in ascending row order) into one matrix: the gather step
+ * of row-panel sharding.  No counterpart in the reference. */
+int bsp_mat_concat_panels(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_mat **out);
+
 /* Product of mats[0..n-1] by the reference's pairwise tree: adjacent pairs at every level,
  * an odd tail is carried to the next level unchanged (= helper2, cu:287-327).  Inputs are
  * borrowed; *out is new (a copy of mats[0] when n == 1).  If log is non-NULL it receives the

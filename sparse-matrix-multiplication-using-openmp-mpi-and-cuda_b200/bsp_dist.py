@@ -170,3 +170,66 @@ def tree_merge(rank, nparts, partial, multiply, send, recv):
                 other = recv(sender)
                 held = multiply(held, other)
     return held if rank == 0 else None
+
+
+def tree_merge_panels(rank, nparts, partial, send, recv, row_weights, multiply_panel, concat):
+    """Step-doubling merge in which every product is ROW-PANEL SHARDED over the ranks of its
+    subtree instead of being computed by the receiving rank alone (the reference's rank 0
+    multiplies the P partials sequentially, cu:569-571, which leaves P-1 ranks idle exactly
+    where the chain is most expensive).  The association tree is unchanged and every output
+    element is still folded by one thread in reference order, so the result is bit-identical.
+
+    For the merge of (g, g+s): ranks g..g+2s-1 all receive left (held by g) and right (held by
+    g+s), each multiplies one block-row panel of left by right (panels balanced by
+    row_weights(left)), the panels are gathered on g and concatenated.
+      send(obj, dst) / recv(src) -> obj        move a matrix
+      row_weights(left) -> 1-D array           estimated work per block row
+      multiply_panel(left, right, lo, hi)      block rows [lo, hi) of left*right
+      concat(list_of_panels)                   one matrix
+    Returns the final product on rank 0, None elsewhere."""
+    held = partial
+    s = 1
+    while s < nparts:
+        for g in range(0, nparts, 2 * s):
+            if g + s >= nparts:
+                continue
+            group = list(range(g, min(g + 2 * s, nparts)))
+            if rank not in group:
+                continue
+            # 1. left from g, right from g+s, to everybody in the group
+            if rank == g:
+                left = held
+                for r in group:
+                    if r != g:
+                        send(left, r)
+            else:
+                left = recv(g)
+            if rank == g + s:
+                right = held
+                for r in group:
+                    if r != g + s:
+                        send(right, r)
+            else:
+                right = recv(g + s)
+            # 2. this rank's panel
+            bounds = balanced_panels(row_weights(left), len(group))
+            me = group.index(rank)
+            panel = multiply_panel(left, right, bounds[me], bounds[me + 1])
+            # 3. gather on g
+            if rank == g:
+                panels = [panel] + [recv(r) for r in group[1:]]
+                held = concat(panels)
+            else:
+                send(panel, g)
+                held = None
+        s *= 2
+    return held if rank == 0 else None
+
+
+def device_row_weights(torch, mat):
+    """Tiles per block row of a device matrix (the balance proxy for row panels)."""
+    nbr = mat.device_view()[0]
+    rp = torch.empty(nbr + 1, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    mat.export_device(rp.data_ptr(), 0, 0)
+    return np.diff(rp.cpu().numpy())

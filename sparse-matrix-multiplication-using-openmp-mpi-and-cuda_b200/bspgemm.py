@@ -57,6 +57,7 @@ _SIGNATURES = {
     "bsp_mat_free": (None, [_VP, _VP]),
     "bsp_spgemm": (C.c_int, [_VP, _VP, _VP, C.POINTER(_VP), C.POINTER(Stats)]),
     "bsp_spgemm_panel": (C.c_int, [_VP, _VP, _VP, C.c_int32, C.c_int32, C.POINTER(_VP), C.POINTER(Stats)]),
+    "bsp_mat_concat_panels": (C.c_int, [_VP, C.POINTER(_VP), C.c_int32, C.POINTER(_VP)]),
     "bsp_chain": (C.c_int, [_VP, C.POINTER(_VP), C.c_int32, C.POINTER(_VP), C.POINTER(Stats), C.c_char_p, C.c_size_t, C.c_int32]),
     "bsp_prune_zero": (C.c_int, [_VP, _VP]),
     "bsp_multiply_host": (C.c_int, [_VP, C.c_int32,
@@ -246,6 +247,14 @@ class Context:
         return (out, buf.value.decode()) if want_log else out
 
     chain = helper2
+
+    def concat_panels(self, panels):
+        """Concatenate block-row panels (ascending, disjoint row ranges of one product)."""
+        n = len(panels)
+        hs = (_VP * n)(*[m.handle for m in panels])
+        h = _VP()
+        self._ck(self.lib.bsp_mat_concat_panels(self.handle, hs, n, C.byref(h)))
+        return Matrix(self, h.value)
 
     def prune_zero_noalloc(self, k, nbrows, nnzb, d_rowptr, d_colidx, d_vals, d_rowptr_out, d_colidx_out, d_vals_out):
         """Zero-tile compaction that allocates nothing (raw device addresses in and out; the

@@ -83,10 +83,11 @@ int clone_mat(bsp_ctx *ctx, const bsp_mat *s, bsp_mat **out)
     BSP_TRY(bsp_alloc(ctx, &m->rowptr, (size_t)s->nbr + 1));
     BSP_TRY(bsp_alloc(ctx, &m->colidx, (size_t)s->nnzb));
     BSP_TRY(bsp_alloc(ctx, &m->vals, (size_t)s->nnzb * kk));
-    BSP_CUDA(ctx, cudaMemcpyAsync(m->rowptr, s->rowptr, ((size_t)s->nbr + 1) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    // cudaMemcpyDefault: the source may live on a peer device (a4 gathers partial products)
+    BSP_CUDA(ctx, cudaMemcpyAsync(m->rowptr, s->rowptr, ((size_t)s->nbr + 1) * 4, cudaMemcpyDefault, ctx->stream));
     if (s->nnzb) {
-        BSP_CUDA(ctx, cudaMemcpyAsync(m->colidx, s->colidx, (size_t)s->nnzb * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-        BSP_CUDA(ctx, cudaMemcpyAsync(m->vals, s->vals, (size_t)s->nnzb * kk * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(m->colidx, s->colidx, (size_t)s->nnzb * 4, cudaMemcpyDefault, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(m->vals, s->vals, (size_t)s->nnzb * kk * 8, cudaMemcpyDefault, ctx->stream));
     }
     return BSP_OK;
 }
@@ -143,6 +144,17 @@ int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
     BSP_CUDA(ctx, cudaDeviceGetDefaultMemPool(&pool, device));
     uint64_t thr = UINT64_MAX;
     BSP_CUDA(ctx, cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    // partial products move device to device (a4 --ranks, cu:471-552): let peers read this pool
+    for (int d = 0; d < ndev; d++) {
+        int can = 0;
+        if (d == device || cudaDeviceCanAccessPeer(&can, d, device) != cudaSuccess || !can) continue;
+        cudaMemAccessDesc desc;
+        memset(&desc, 0, sizeof(desc));
+        desc.location.type = cudaMemLocationTypeDevice;
+        desc.location.id = d;
+        desc.flags = cudaMemAccessFlagsProtReadWrite;
+        if (cudaMemPoolSetAccess(pool, &desc, 1) != cudaSuccess) cudaGetLastError(); // fall back to staged copies
+    }
     return BSP_OK;
 }
 
@@ -323,6 +335,32 @@ int bsp_spgemm_panel(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t r
 {
     if (ctx && row_lo > row_hi) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm_panel: row_lo > row_hi");
     return spgemm_impl(ctx, A, B, row_lo, row_hi, C, stats);
+}
+
+int bsp_mat_concat_panels(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_mat **out)
+{
+    if (!ctx || !out) return BSP_ERR_ARG;
+    *out = nullptr;
+    if (n < 1 || !panels) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_concat_panels: no panels");
+    int64_t total = 0;
+    for (int i = 0; i < n; i++) {
+        if (!valid_mat(panels[i])) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_concat_panels: panel %d is null", i);
+        if (panels[i]->k != panels[0]->k || panels[i]->nbr != panels[0]->nbr)
+            BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_concat_panels: panel %d has another shape", i);
+        total += panels[i]->nnzb;
+    }
+    if (total > 0x7fffffffLL) BSP_FAIL(ctx, BSP_ERR_LIMIT, "more than 2^31-1 tiles");
+    BSP_CUDA(ctx, cudaSetDevice(ctx->device));
+    bsp_mat *m = nullptr;
+    int32_t nbc = 0;
+    for (int i = 0; i < n; i++) nbc = panels[i]->nbc > nbc ? panels[i]->nbc : nbc;
+    BSP_TRY(new_empty_like(ctx, panels[0]->rows, panels[0]->cols, panels[0]->k, panels[0]->nbr, nbc, &m));
+    *out = m;
+    m->nnzb = total;
+    BSP_TRY(bsp_alloc(ctx, &m->rowptr, (size_t)m->nbr + 1));
+    BSP_TRY(bsp_alloc(ctx, &m->colidx, (size_t)total));
+    BSP_TRY(bsp_alloc(ctx, &m->vals, (size_t)total * m->k * m->k));
+    return bsp_concat_panels_device(ctx, panels, n, m);
 }
 
 int bsp_chain(bsp_ctx *ctx, bsp_mat *const *mats, int32_t n, bsp_mat **out, bsp_stats *stats, char *log,

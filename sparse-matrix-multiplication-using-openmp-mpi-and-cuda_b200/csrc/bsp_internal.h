@@ -139,6 +139,7 @@ int bsp_numeric(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
                 uint64_t *c_vals, int64_t *exact_refolds, int32_t *path);
 
 int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m);
+int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_mat *out);
 int bsp_expand_rows(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_brow);
 int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,
                    const int32_t *d_brow, const int32_t *d_bcol, const uint64_t *d_vals,

@@ -116,6 +116,12 @@ __global__ void remap_rowptr_kernel(const int32_t *__restrict__ rowptr, int32_t 
     if (r <= nbr) rowptr_out[r] = pos[rowptr[r]];
 }
 
+__global__ void add_rowptr_kernel(const int32_t *__restrict__ src, int32_t n, int32_t *__restrict__ dst)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < n) dst[r] += src[r];
+}
+
 inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads > 0 ? (n + threads - 1) / threads : 1); }
 
 } // namespace
@@ -223,5 +229,27 @@ int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m)
     }
     bsp_release(ctx, keep);
     bsp_release(ctx, pos);
+    return BSP_OK;
+}
+
+int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_mat *out)
+{
+    // Panel i has tiles only in its own row range, so its rowptr is 0 before the range and
+    // nnzb_i after it: the row pointers of the concatenation are the element-wise sum, and
+    // colidx / vals are the panels' arrays back to back.
+    const int nbr = out->nbr;
+    const size_t kk = (size_t)out->k * out->k;
+    BSP_CUDA(ctx, cudaMemsetAsync(out->rowptr, 0, ((size_t)nbr + 1) * sizeof(int32_t), ctx->stream));
+    int64_t off = 0;
+    for (int i = 0; i < n; i++) {
+        const bsp_mat *p = panels[i];
+        add_rowptr_kernel<<<blocks_for((int64_t)nbr + 1, 256), 256, 0, ctx->stream>>>(p->rowptr, nbr + 1, out->rowptr);
+        BSP_LAUNCH_CHECK(ctx);
+        if (p->nnzb) {
+            BSP_CUDA(ctx, cudaMemcpyAsync(out->colidx + off, p->colidx, (size_t)p->nnzb * 4, cudaMemcpyDefault, ctx->stream));
+            BSP_CUDA(ctx, cudaMemcpyAsync(out->vals + (size_t)off * kk, p->vals, (size_t)p->nnzb * kk * 8, cudaMemcpyDefault, ctx->stream));
+        }
+        off += p->nnzb;
+    }
     return BSP_OK;
 }

@@ -43,7 +43,24 @@ def _payload_to_omat(pl):
     return orc.OMat.from_coo(rows, cols, k, br, pl.colidx.numpy(), pl.vals.numpy().view(np.uint64))
 
 
-def _worker(rank, world, port, n_mats, k, G, outdir):
+def _row_slice(m, lo, hi):
+    br, bc, v = m.coo()
+    keep = (br >= lo) & (br < hi)
+    return orc.OMat.from_coo(m.rows, m.cols, m.k, br[keep], bc[keep], v[keep])
+
+
+def _concat(panels):
+    parts = [p.coo() for p in panels]
+    return orc.OMat.from_coo(panels[0].rows, panels[0].cols, panels[0].k, np.concatenate([p[0] for p in parts]),
+                             np.concatenate([p[1] for p in parts]), np.concatenate([p[2] for p in parts]))
+
+
+def _weights(m):
+    br = m.coo()[0]
+    return np.bincount(br, minlength=(int(br.max()) + 1 if br.size else 1))
+
+
+def _worker(rank, world, port, n_mats, k, G, outdir, panels=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -53,11 +70,15 @@ def _worker(rank, world, port, n_mats, k, G, outdir):
         if rank < len(parts):
             s, e = parts[rank]
             partial = orc.chain(mats[s:e + 1])[0]
-        res = bsp_dist.tree_merge(
-            rank, len(parts), partial,
-            multiply=lambda a, b: orc.multiply(a, b)[0],
-            send=lambda m, dst: bsp_dist.send_payload(dist, _omat_to_payload(m), dst),
-            recv=lambda src: _payload_to_omat(bsp_dist.recv_payload(dist, torch, src, "cpu")))
+        send = lambda m, dst: bsp_dist.send_payload(dist, _omat_to_payload(m), dst)  # noqa: E731
+        recv = lambda src: _payload_to_omat(bsp_dist.recv_payload(dist, torch, src, "cpu"))  # noqa: E731
+        if panels:
+            res = bsp_dist.tree_merge_panels(
+                rank, len(parts), partial, send, recv, _weights,
+                multiply_panel=lambda a, b, lo, hi: orc.multiply(_row_slice(a, lo, hi), b)[0], concat=_concat)
+        else:
+            res = bsp_dist.tree_merge(rank, len(parts), partial, multiply=lambda a, b: orc.multiply(a, b)[0],
+                                      send=send, recv=recv)
         if rank == 0:
             res.prune_zero().write(os.path.join(outdir, "matrix"))
         dist.barrier()
@@ -65,11 +86,11 @@ def _worker(rank, world, port, n_mats, k, G, outdir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,n_mats", [(2, 5), (2, 1), (3, 7)])
-def test_tree_merge_over_gloo_matches_rank_oracle(world, n_mats):
+@pytest.mark.parametrize("world,n_mats,panels", [(2, 5, False), (2, 1, False), (3, 7, False), (2, 5, True), (4, 9, True)])
+def test_tree_merge_over_gloo_matches_rank_oracle(world, n_mats, panels):
     k, G = 2, 8
     with tempfile.TemporaryDirectory() as d:
-        mp.spawn(_worker, args=(world, _free_port(), n_mats, k, G, d), nprocs=world, join=True)
+        mp.spawn(_worker, args=(world, _free_port(), n_mats, k, G, d, panels), nprocs=world, join=True)
         mats = [orc.OMat.from_coo(*bsp_gen.random_matrix(G * k, G * k, k, 0.3, 3000 + i, "edgy")) for i in range(n_mats)]
         want = orc.chain(mats, ranks=world)[0].prune_zero()
         p = os.path.join(d, "want")

@@ -50,9 +50,13 @@ parts = bsp_dist.split_chain(n, world)
 s, e = parts[rank]
 mats = [ctx.matrix_from_coo(*bsp_gen.random_matrix(G * k, G * k, k, 0.08, 8100 + i, "edgy")) for i in range(s, e + 1)]
 partial = ctx.helper2(mats)
-res = bsp_dist.tree_merge(rank, len(parts), partial, lambda a, b: ctx.helper(a, b),
-                          lambda m, dst: bsp_dist.send_payload(dist, bsp_dist.matrix_to_payload(torch, m), dst),
-                          lambda src: bsp_dist.payload_to_matrix(torch, ctx, bsp_dist.recv_payload(dist, torch, src, "cuda")))
+send = lambda m, dst: bsp_dist.send_payload(dist, bsp_dist.matrix_to_payload(torch, m), dst)
+recv = lambda src: bsp_dist.payload_to_matrix(torch, ctx, bsp_dist.recv_payload(dist, torch, src, "cuda"))
+if sys.argv[4] == "panels":
+    res = bsp_dist.tree_merge_panels(rank, len(parts), partial, send, recv, lambda m: bsp_dist.device_row_weights(torch, m),
+                                     lambda a, b, lo, hi: ctx.helper(a, b, panel=(lo, hi)), ctx.concat_panels)
+else:
+    res = bsp_dist.tree_merge(rank, len(parts), partial, lambda a, b: ctx.helper(a, b), send, recv)
 if rank == 0:
     res.prune_zero().write_text(sys.argv[3])
 dist.barrier()
@@ -61,7 +65,8 @@ dist.destroy_process_group()
 
 
 @pytest.mark.skipif("_ngpu() < 2")
-def test_nccl_tree_merge_two_ranks():
+@pytest.mark.parametrize("mode", ["rank0", "panels"])
+def test_nccl_tree_merge_two_ranks(mode):
     k, G, n = 4, 40, 9
     pkg = os.path.dirname(bspgemm.__file__)
     with tempfile.TemporaryDirectory() as d:
@@ -70,7 +75,7 @@ def test_nccl_tree_merge_two_ranks():
         out = os.path.join(d, "matrix")
         p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                             "--master-addr", "127.0.0.1", "--master-port", "29611", script, pkg,
-                            os.path.join(util.ROOT, "oracle"), out], stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+                            os.path.join(util.ROOT, "oracle"), out, mode], stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
         assert p.returncode == 0, p.stderr.decode()[-3000:]
         mats = [orc.OMat.from_coo(*bsp_gen.random_matrix(G * k, G * k, k, 0.08, 8100 + i, "edgy")) for i in range(n)]
         want = orc.chain(mats, ranks=2)[0].prune_zero()

@@ -314,3 +314,16 @@ def test_symbolic_row_classes_and_generic_numeric(ctx):
     finally:
         os.environ.pop("BSP_SYM_CAPS", None)
         os.environ.pop("BSP_FORCE_GENERIC", None)
+
+
+def test_concat_panels(ctx):
+    k, G = 4, 120
+    a = bsp_gen.random_matrix(G * k, G * k, k, 0.06, 91, "edgy")
+    b = bsp_gen.random_matrix(G * k, G * k, k, 0.06, 92, "edgy")
+    A, B = dev(ctx, a), dev(ctx, b)
+    full = ctx.helper(A, B).to_coo()
+    bounds = [0, 1, 50, 50, 99, G]
+    parts = [ctx.helper(A, B, panel=(bounds[i], bounds[i + 1])) for i in range(5)]
+    got = ctx.concat_panels(parts).to_coo()
+    for x, y in zip(got, full):
+        assert np.array_equal(x, y)
