@@ -97,6 +97,11 @@ int bsp_mat_device_view(const bsp_mat *m, int32_t *nbrows, int32_t *nbcols,
 int bsp_mat_export_device(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_rowptr, int32_t *d_colidx,
                           uint64_t *d_vals);
 
+/* Copy a matrix into another context, possibly on another GPU of the same process (peer copy
+ * over NVLink when available): how a4 gathers the partial products on device 0 (replaces
+ * MPI_Send / MPI_Recv + map rebuild, cu:471-551). */
+int bsp_mat_copy_to_ctx(bsp_ctx *src_ctx, const bsp_mat *m, bsp_ctx *dst_ctx, bsp_mat **out);
+
 /* Build a matrix from a device CSR-of-blocks view (arrays are copied).  The receiving side
  * of the partial-product exchange that replaces MPI_Recv + map rebuild (cu:513-551). */
 int bsp_mat_from_device_bcsr(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows,

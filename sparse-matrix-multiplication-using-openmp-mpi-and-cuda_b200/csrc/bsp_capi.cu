@@ -144,17 +144,6 @@ int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
     BSP_CUDA(ctx, cudaDeviceGetDefaultMemPool(&pool, device));
     uint64_t thr = UINT64_MAX;
     BSP_CUDA(ctx, cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
-    // partial products move device to device (a4 --ranks, cu:471-552): let peers read this pool
-    for (int d = 0; d < ndev; d++) {
-        int can = 0;
-        if (d == device || cudaDeviceCanAccessPeer(&can, d, device) != cudaSuccess || !can) continue;
-        cudaMemAccessDesc desc;
-        memset(&desc, 0, sizeof(desc));
-        desc.location.type = cudaMemLocationTypeDevice;
-        desc.location.id = d;
-        desc.flags = cudaMemAccessFlagsProtReadWrite;
-        if (cudaMemPoolSetAccess(pool, &desc, 1) != cudaSuccess) cudaGetLastError(); // fall back to staged copies
-    }
     return BSP_OK;
 }
 
@@ -292,6 +281,32 @@ int bsp_mat_export_device(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_rowptr, int
     if (d_vals && m->nnzb)
         BSP_CUDA(ctx, cudaMemcpyAsync(d_vals, m->vals, (size_t)m->nnzb * kk * 8, cudaMemcpyDeviceToDevice, ctx->stream));
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSP_OK;
+}
+
+int bsp_mat_copy_to_ctx(bsp_ctx *src_ctx, const bsp_mat *m, bsp_ctx *dst_ctx, bsp_mat **out)
+{
+    if (!src_ctx || !dst_ctx || !out) return BSP_ERR_ARG;
+    *out = nullptr;
+    if (!valid_mat(m)) BSP_FAIL(dst_ctx, BSP_ERR_ARG, "bsp_mat_copy_to_ctx: null matrix");
+    BSP_CUDA(src_ctx, cudaSetDevice(src_ctx->device));
+    BSP_CUDA(src_ctx, cudaStreamSynchronize(src_ctx->stream)); // the source must be complete
+    BSP_CUDA(dst_ctx, cudaSetDevice(dst_ctx->device));
+    bsp_mat *c = nullptr;
+    BSP_TRY(new_empty_like(dst_ctx, m->rows, m->cols, m->k, m->nbr, m->nbc, &c));
+    *out = c;
+    c->nnzb = m->nnzb;
+    const size_t kk = (size_t)m->k * m->k;
+    BSP_TRY(bsp_alloc(dst_ctx, &c->rowptr, (size_t)m->nbr + 1));
+    BSP_TRY(bsp_alloc(dst_ctx, &c->colidx, (size_t)m->nnzb));
+    BSP_TRY(bsp_alloc(dst_ctx, &c->vals, (size_t)m->nnzb * kk));
+    const int sd = m->device, dd = dst_ctx->device;
+    BSP_CUDA(dst_ctx, cudaMemcpyPeerAsync(c->rowptr, dd, m->rowptr, sd, ((size_t)m->nbr + 1) * 4, dst_ctx->stream));
+    if (m->nnzb) {
+        BSP_CUDA(dst_ctx, cudaMemcpyPeerAsync(c->colidx, dd, m->colidx, sd, (size_t)m->nnzb * 4, dst_ctx->stream));
+        BSP_CUDA(dst_ctx, cudaMemcpyPeerAsync(c->vals, dd, m->vals, sd, (size_t)m->nnzb * kk * 8, dst_ctx->stream));
+    }
+    BSP_CUDA(dst_ctx, cudaStreamSynchronize(dst_ctx->stream));
     return BSP_OK;
 }
 

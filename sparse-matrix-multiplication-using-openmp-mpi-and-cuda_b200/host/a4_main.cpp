@@ -145,15 +145,8 @@ int main(int argc, char **argv)
             // gather the partial products on device 0 (replaces MPI_Send/Recv, cu:471-552)
             std::vector<bsp_mat *> parts;
             for (auto &r : ranks) {
-                int32_t rows, cols, kk, nbr, nbc;
-                int64_t nnzb;
-                const int32_t *rp, *ci;
-                const uint64_t *v;
-                bsp_mat_info(r.partial, &rows, &cols, &kk, &nnzb);
-                bsp_mat_device_view(r.partial, &nbr, &nbc, &rp, &ci, &v);
-                bsp_ctx_sync(r.ctx);
                 bsp_mat *m = nullptr;
-                int e = bsp_mat_from_device_bcsr(probe, rows, cols, kk, nbr, nbc, nnzb, rp, ci, v, &m);
+                int e = bsp_mat_copy_to_ctx(r.ctx, r.partial, probe, &m);
                 if (e) { fprintf(stderr, "a4: gather: %s\n", bsp_last_error(probe)); rc = 3; break; }
                 parts.push_back(m);
             }
