@@ -218,13 +218,15 @@ __device__ __forceinline__ int a_chunk_offset(int r, int i)
     return r * (K * 8) + i * 16;
 }
 
-__device__ __forceinline__ void cp_async16_ca(unsigned smem_addr, const void *gsrc)
+// 16-byte asynchronous copies; nbytes = 16 copies, nbytes = 0 reads nothing and zero-fills
+// (used for groups that have run out of tile products: no branch, no global traffic)
+__device__ __forceinline__ void cp_async16_ca(unsigned smem_addr, const void *gsrc, unsigned nbytes)
 {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(smem_addr), "l"(gsrc) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;\n" ::"r"(smem_addr), "l"(gsrc), "r"(nbytes) : "memory");
 }
-__device__ __forceinline__ void cp_async16_cg(unsigned smem_addr, const void *gsrc)
+__device__ __forceinline__ void cp_async16_cg(unsigned smem_addr, const void *gsrc, unsigned nbytes)
 {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_addr), "l"(gsrc) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(smem_addr), "l"(gsrc), "r"(nbytes) : "memory");
 }
 __device__ __forceinline__ ulonglong2 lds128(unsigned smem_addr)
 {
@@ -283,8 +285,9 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
 
     // The whole warp copies the tiles of all its groups for one step into stage ST: every
     // cp.async instruction moves 512 contiguous bytes (one k=8 tile, or four k=4 tiles).
-    // (ai, bi) = this group's pair for that step.  A group that has run out of steps repeats
-    // its last pair (or tile 0): the bytes land in a stage nobody reads.
+    // (ai, bi) = this group's pair for that step; a negative ai marks a group that has run out of
+    // steps: its copies become zero-size (nothing is read; thousands of idle groups re-reading
+    // one dummy tile would serialise on a single L2 line).
     auto issue = [&](int ST, int ai, int bi) {
         const unsigned sbase = wbase + ST * Cfg::STAGE_BYTES;
 #pragma unroll
@@ -292,12 +295,12 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
             const int src_lane = (q0 + cq) * TPT;
             const int qa = __shfl_sync(0xffffffffu, ai, src_lane);
             const int qb = __shfl_sync(0xffffffffu, bi, src_lane);
+            const unsigned nbytes = qa < 0 ? 0u : 16u;
+            const size_t ia = (size_t)(unsigned)(qa & 0x7fffffff), ib = (size_t)(unsigned)qb;
 #pragma unroll
             for (int part = 0; part < Cfg::IPT; part++) {
-                cp_async16_ca(sbase + q0 * Cfg::GROUP_STRIDE + dstA[part],
-                              a_lane + (size_t)(unsigned)qa * Cfg::TILE_BYTES + part * 512);
-                cp_async16_cg(sbase + q0 * Cfg::GROUP_STRIDE + dstB[part],
-                              b_lane + (size_t)(unsigned)qb * Cfg::TILE_BYTES + part * 512);
+                cp_async16_ca(sbase + q0 * Cfg::GROUP_STRIDE + dstA[part], a_lane + ia * Cfg::TILE_BYTES + part * 512, nbytes);
+                cp_async16_cg(sbase + q0 * Cfg::GROUP_STRIDE + dstB[part], b_lane + ib * Cfg::TILE_BYTES + part * 512, nbytes);
             }
         }
     };
@@ -313,7 +316,7 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
     { const int2 pr = __ldcs(prs); nx = pr.x; ny = pr.y; }
 #pragma unroll
     for (int st = 0; st < STAGES - 1; st++) {
-        issue(st, nx, ny & 0x7fffffff);
+        issue(st, st < n ? nx : (nx | (int)0x80000000), ny & 0x7fffffff);
         lastq |= (st < n && ny < 0 ? 1u : 0u) << st;
         { const int2 pr = __ldcs(prs + min(st + 1, n_last)); nx = pr.x; ny = pr.y; }
         cp_async_commit();
@@ -335,7 +338,7 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
         __syncwarp();                // ... and everybody else's; everybody is done reading step k-1's stage
         {
             const int kk = k + (STAGES - 1);
-            issue((ST + STAGES - 1) % STAGES, nx, ny & 0x7fffffff);
+            issue((ST + STAGES - 1) % STAGES, kk < n ? nx : (nx | (int)0x80000000), ny & 0x7fffffff);
             lastq |= (kk < n && ny < 0 ? 1u : 0u) << (STAGES - 1);
             { const int2 pr = __ldcs(prs + min(kk + 1, n_last)); nx = pr.x; ny = pr.y; }
             cp_async_commit();
@@ -407,12 +410,12 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
     cp_async_wait<0>();
 }
 
-struct NumericTuning { int Q; int panel_mb; int stages; int warps; };
+struct NumericTuning { int Q; int panel_mb; int stages; int warps; bool q_forced; };
 
 NumericTuning numeric_tuning()
 {
-    NumericTuning tn = {96, 1 << 20, 2, 4}; // panels off by default: measured no gain on cfg2 (see profiles/)
-    if (const char *e = getenv("BSP_NUM_Q")) { int v = atoi(e); if (v >= 1) tn.Q = v; }
+    NumericTuning tn = {96, 1 << 20, 2, 4, false}; // panels off by default: measured no gain on cfg2 (see profiles/)
+    if (const char *e = getenv("BSP_NUM_Q")) { int v = atoi(e); if (v >= 1) { tn.Q = v; tn.q_forced = true; } }
     if (const char *e = getenv("BSP_NUM_PANEL_MB")) { int v = atoi(e); if (v >= 1) tn.panel_mb = v; }
     if (const char *e = getenv("BSP_NUM_STAGES")) { int v = atoi(e); if (v == 2 || v == 3) tn.stages = v; }
     if (const char *e = getenv("BSP_NUM_WARPS")) { int v = atoi(e); if (v == 4 || v == 8) tn.warps = v; }
@@ -432,7 +435,13 @@ int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_
     if (npanels > 64) npanels = 64;
     if (npanels > B->nbc) npanels = B->nbc > 0 ? B->nbc : 1;
     const int panel_w = (B->nbc + npanels - 1) / npanels;
-    const int Q = tn.Q;
+    // chunk size: at least a few output tiles' worth of products, so that a chunk is rarely a
+    // single over-long tile next to empty neighbours (dense chain levels fold 100+ pairs per tile)
+    int Q = tn.Q;
+    if (!tn.q_forced && sym->nnzb_c > 0) {
+        const int64_t avg4 = 4 * (sym->nprod / sym->nnzb_c);
+        if (avg4 > Q) Q = (int)(avg4 > 8192 ? 8192 : avg4);
+    }
     const int64_t nseg = (int64_t)nbr * npanels;
     const int64_t max_chunks64 = sym->nprod / Q + nseg + 1;
     if (max_chunks64 > 0x7fffff00LL) BSP_FAIL(ctx, BSP_ERR_LIMIT, "numeric pass: too many chunks");
