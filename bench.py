@@ -297,6 +297,57 @@ def run_chain(torch, dist, ctx, rank, world, steps, warmup):
 
 
 # --------------------------------------------------------------------------------------------
+# secondary figure: power-law pattern, row-panel sharded single product (BASELINE.json configs[3])
+# --------------------------------------------------------------------------------------------
+
+def run_rmat(torch, dist, ctx, rank, world, steps):
+    """R-MAT block pattern (scale 15 = 32768 block rows, edge factor 16, a/b/c/d = .57/.19/.19/.05),
+    n=262144, k=8.  Every rank holds A and B (same seeds), multiplies ONE block-row panel of A by B;
+    panels are contiguous and balanced by tile products per block row.  No collective on the data
+    path; the product stays distributed by panels.  Strong scaling: the product is fixed."""
+    import bsp_dist
+    import bsp_gen
+    import bspgemm
+    scale, k = 15, 8
+    G = 1 << scale
+    mats = []
+    for seed in (11, 12):
+        br, bc = bsp_gen.rmat_pattern(scale, 16, seed)
+        v = bsp_gen.values(seed, br.size * k * k, "u64").reshape(-1, k, k)
+        mats.append((G * k, G * k, k, br, bc, v))
+    rowlen_b = np.bincount(mats[1][3], minlength=G)
+    row_work = np.bincount(mats[0][3], weights=rowlen_b[mats[0][4]], minlength=G)
+    bounds = bsp_dist.balanced_panels(row_work, world)
+    A, B = ctx.matrix_from_coo(*mats[0]), ctx.matrix_from_coo(*mats[1])
+    st = bspgemm.Stats()
+    ms = []
+    for i in range(steps + 2):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ctx.helper(A, B, stats=st, panel=(bounds[rank], bounds[rank + 1])).free()
+        if i >= 2:
+            ms.append(st.ms_total)
+    mine = torch.tensor([sum(ms) / len(ms), float(st.nprod), float(st.nnzb_c)], dtype=torch.float64, device="cuda")
+    allv = [torch.zeros_like(mine) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(allv, mine)
+    else:
+        allv = [mine]
+    A.free(); B.free()
+    if rank != 0:
+        return None
+    t = [x[0].item() for x in allv]
+    nprod = sum(x[1].item() for x in allv)
+    return {"ms": max(t), "unit": "ms", "n_gpus": world, "scaling": "strong",
+            "workload": "R-MAT block pattern scale %d (n=%d, k=%d), A*B row-panel sharded x%d, panels balanced by tile products"
+                        % (scale, G * k, k, world),
+            "per_gpu_ms": [round(x, 3) for x in t], "max_over_mean": max(t) / (sum(t) / len(t)),
+            "nprod_total": int(nprod), "nnzb_c_total": int(sum(x[2].item() for x in allv)),
+            "useful_gflops": 2.0 * k ** 3 * nprod / (max(t) * 1e-3) / 1e9}
+
+
+# --------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------
 
@@ -311,6 +362,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 3)")
     ap.add_argument("--no-chain", action="store_true")
+    ap.add_argument("--rmat", action="store_true", help="also run the R-MAT row-panel figure (default: only when --gpus > 1)")
+    ap.add_argument("--no-rmat", action="store_true")
     ap.add_argument("--chain-steps", type=int, default=2)
     args = ap.parse_args()
     if args.impl == "reference":
@@ -415,6 +468,10 @@ def main():
             A.free(); B.free()
             chain = run_chain(torch, dist, ctx, rank, world, max(1, args.chain_steps), 1)
 
+        rmat = None
+        if (args.rmat or world > 1) and not args.no_rmat:
+            rmat = run_rmat(torch, dist, ctx, rank, world, 3)
+
         if rank == 0:
             peak, peak_src = measured_peak()
             alg = algorithmic_bytes(st.nnzb_a, st.nnzb_b, st.nnzb_c, G, k)
@@ -444,6 +501,8 @@ def main():
                 line["e2e"] = e2e
             if chain:
                 line["chain"] = chain
+            if rmat:
+                line["rmat_panels"] = rmat
             if world == 1 and not args.no_cpu:
                 try:
                     cb = cpu_reference_measure(n, k, d, steps=1, warmup=0)
