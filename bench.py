@@ -35,6 +35,8 @@ WORKLOADS = {
     "cfg1": (1024, 4, 0.05, "u64"),
     "mid": (16384, 8, 0.01, "u64"),
 }
+# DRAM bytes of one numeric-kernel launch from the committed `ncu --set full` capture (not measured live)
+NCU_TRAFFIC_BYTES = {("cfg2", 8): 30182856000 + 19197000000}
 METRIC = "spgemm_useful_gflops"
 UNIT = "GFLOP/s"
 
@@ -506,7 +508,9 @@ def main():
                            "numeric_path": st.numeric_path, "exact_refolds": st.exact_refolds},
                 "phases_ms": {"symbolic": s_ms, "numeric": k_ms},
                 "roofline": {"bound": "hbm", "kernel": "numeric pass (tile multiply-accumulate)", "achieved": ach,
-                             "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                             "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                             "traffic": NCU_TRAFFIC_BYTES.get((args.workload, world == 1 and st.numeric_path)),
+                             "traffic_source": "profiles/r01_ncu_full_v5_raw.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
                              "algorithmic_bytes": alg, "peak_source": peak_src,
                              "useful_u64_mac_per_s": k ** 3 * st.nprod / (k_ms * 1e-3)},
                 "roofline_symbolic": {"bound": "hbm", "achieved": sb / (s_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",

@@ -74,10 +74,16 @@ __device__ __forceinline__ int build_row_bitmap(uint32_t *bm, int words, const i
     return nprod;
 }
 
+// Light rows (few tile products) are counted by one warp each; a row whose product count
+// exceeds SYM_HEAVY (R-MAT hubs, dense chain levels) is appended to a list and counted by a
+// whole CTA in sym_count_heavy_kernel, so that one warp never walks 10^5 products alone.
+constexpr int SYM_HEAVY = 4096;
+
 __global__ void __launch_bounds__(SYM_THREADS)
 sym_count_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t *__restrict__ a_colidx, int b_nbr,
                  const int32_t *__restrict__ b_rowptr, const int32_t *__restrict__ b_colidx, int words, int row_lo,
-                 int row_hi, int32_t *__restrict__ row_cnt, int32_t *__restrict__ row_prod)
+                 int row_hi, int32_t *__restrict__ row_cnt, int32_t *__restrict__ row_prod,
+                 int32_t *__restrict__ heavy_list, int32_t *__restrict__ heavy_count)
 {
     extern __shared__ uint32_t smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -85,15 +91,68 @@ sym_count_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t 
     for (int row = blockIdx.x * SYM_WARPS + warp; row < a_nbr; row += gridDim.x * SYM_WARPS) {
         int cnt = 0, nprod = 0;
         if (row >= row_lo && row < row_hi && a_rowptr[row + 1] > a_rowptr[row]) {
-            nprod = build_row_bitmap(bm, words, a_rowptr, a_colidx, b_nbr, b_rowptr, b_colidx, row);
-            for (int w = lane; w < words; w += 32) cnt += __popc(bm[w]);
-            cnt = warp_sum(cnt);
-            __syncwarp();
+            // tile products of the row: lanes over the A entries
+            const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
+            for (int p = a0 + lane; p < a1; p += 32) {
+                const int j = a_colidx[p];
+                if (j < b_nbr) nprod += b_rowptr[j + 1] - b_rowptr[j];
+            }
+            nprod = warp_sum(nprod);
+            if (nprod > SYM_HEAVY) {
+                if (lane == 0) heavy_list[atomicAdd(heavy_count, 1)] = row;
+                cnt = -1; // filled in by sym_count_heavy_kernel
+            } else if (nprod > 0) {
+                build_row_bitmap(bm, words, a_rowptr, a_colidx, b_nbr, b_rowptr, b_colidx, row);
+                for (int w = lane; w < words; w += 32) cnt += __popc(bm[w]);
+                cnt = warp_sum(cnt);
+                __syncwarp();
+            }
         }
         if (lane == 0) {
-            row_cnt[row] = cnt;
+            if (cnt >= 0) row_cnt[row] = cnt;
             row_prod[row] = nprod;
         }
+    }
+}
+
+constexpr int HEAVY_THREADS = 512;
+
+__global__ void __launch_bounds__(HEAVY_THREADS)
+sym_count_heavy_kernel(const int32_t *__restrict__ heavy_list, const int32_t *__restrict__ heavy_count,
+                       const int32_t *__restrict__ a_rowptr, const int32_t *__restrict__ a_colidx, int b_nbr,
+                       const int32_t *__restrict__ b_rowptr, const int32_t *__restrict__ b_colidx, int words,
+                       int32_t *__restrict__ row_cnt)
+{
+    extern __shared__ uint32_t bm[];
+    __shared__ int warp_cnt[HEAVY_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = HEAVY_THREADS / 32;
+    const int nheavy = *heavy_count;
+    for (int idx = blockIdx.x; idx < nheavy; idx += gridDim.x) {
+        const int row = heavy_list[idx];
+        for (int w = tid; w < words; w += HEAVY_THREADS) bm[w] = 0u;
+        __syncthreads();
+        const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
+        for (int p = a0 + warp; p < a1; p += nwarp) { // warps over A entries, lanes over B row j
+            const int j = a_colidx[p];
+            if (j >= b_nbr) continue;
+            const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+            for (int q = b0 + lane; q < b1; q += 32) {
+                const int c = b_colidx[q];
+                atomicOr(&bm[c >> 5], 1u << (c & 31));
+            }
+        }
+        __syncthreads();
+        int cnt = 0;
+        for (int w = tid; w < words; w += HEAVY_THREADS) cnt += __popc(bm[w]);
+        cnt = warp_sum(cnt);
+        if (lane == 0) warp_cnt[warp] = cnt;
+        __syncthreads();
+        if (tid == 0) {
+            int t = 0;
+            for (int i = 0; i < nwarp; i++) t += warp_cnt[i];
+            row_cnt[row] = t;
+        }
+        __syncthreads();
     }
 }
 
@@ -357,6 +416,20 @@ sym_fill_global_kernel(const int32_t *__restrict__ rowlist, const int32_t *__res
     }
     __threadfence_block();
     __syncthreads();
+    // largest pair count of a tile (decides how the pairs are put in order below)
+    __shared__ int maxcnt_sh;
+    if (tid == 0) maxcnt_sh = 0;
+    __syncthreads();
+    {
+        int m = 0;
+        for (int t = tid; t < T; t += FILLG_THREADS) m = max(m, (int)pair_ptr[(size_t)cbase + t]);
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, 16)); m = max(m, __shfl_xor_sync(0xffffffffu, m, 8));
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, 4)); m = max(m, __shfl_xor_sync(0xffffffffu, m, 2));
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, 1));
+        if (lane == 0) atomicMax(&maxcnt_sh, m);
+    }
+    __syncthreads();
+    const bool few = maxcnt_sh <= FILL_SORT_MAX;
     // in-place exclusive scan of the row's counts by warp 0 (rows this large are rare)
     if (warp == 0) {
         unsigned long long run = (unsigned long long)row_prod_ptr[row];
@@ -375,20 +448,51 @@ sym_fill_global_kernel(const int32_t *__restrict__ rowlist, const int32_t *__res
     }
     __threadfence_block();
     __syncthreads();
-    for (int p = a0; p < a1; p++) {
-        const int j = a_colidx[p];
-        if (j >= b_nbr) continue;
-        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
-        for (int q = b0 + tid; q < b1; q += FILLG_THREADS) {
-            const int c = b_colidx[q];
-            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
-            volatile unsigned long long *cu = &pair_ptr[(size_t)cbase + t];
-            const unsigned long long pos = *cu;
-            *cu = pos + 1ull;
-            pairs[pos] = make_int2(p, q);
+    if (few) {
+        // every tile has few pairs: place everything at once (atomic cursor bump, any order),
+        // then order each tile's pairs by A index (= ascending j) with a tiny insertion sort
+        for (int p = a0 + warp; p < a1; p += nwarp) {
+            const int j = a_colidx[p];
+            if (j >= b_nbr) continue;
+            const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+            for (int q = b0 + lane; q < b1; q += 32) {
+                const int c = b_colidx[q];
+                const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+                const unsigned long long pos = atomicAdd(&pair_ptr[(size_t)cbase + t], 1ull);
+                pairs[pos] = make_int2(p, q);
+            }
         }
         __threadfence_block();
         __syncthreads();
+        for (int t = tid; t < T; t += FILLG_THREADS) {
+            const long long e1 = (long long)((volatile unsigned long long *)pair_ptr)[(size_t)cbase + t];
+            const long long s1 = t ? (long long)((volatile unsigned long long *)pair_ptr)[(size_t)cbase + t - 1]
+                                   : (long long)row_prod_ptr[row];
+            for (long long i = s1 + 1; i < e1; i++) {
+                const int2 v = pairs[i];
+                long long jx = i - 1;
+                while (jx >= s1 && pairs[jx].x > v.x) { pairs[jx + 1] = pairs[jx]; jx--; }
+                pairs[jx + 1] = v;
+            }
+        }
+        __threadfence_block();
+        __syncthreads();
+    } else {
+        for (int p = a0; p < a1; p++) {
+            const int j = a_colidx[p];
+            if (j >= b_nbr) continue;
+            const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+            for (int q = b0 + tid; q < b1; q += FILLG_THREADS) {
+                const int c = b_colidx[q];
+                const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+                volatile unsigned long long *cu = &pair_ptr[(size_t)cbase + t];
+                const unsigned long long pos = *cu;
+                *cu = pos + 1ull;
+                pairs[pos] = make_int2(p, q);
+            }
+            __threadfence_block();
+            __syncthreads();
+        }
     }
     // slots now hold tile ends: mark the last pair of every tile (sign bit of .y) ...
     for (int t = tid; t < T; t += FILLG_THREADS) {
@@ -444,17 +548,18 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
                  "symbolic pass: block-column space %d needs %zu B of shared memory per CTA (limit 204800 B, "
                  "i.e. at most 204800 block columns)", B->nbc, smem_count);
 
-    int32_t *row_cnt = nullptr, *row_prod = nullptr, *lists = nullptr, *counts = nullptr;
+    int32_t *row_cnt = nullptr, *row_prod = nullptr, *lists = nullptr, *counts = nullptr, *heavy = nullptr;
     int64_t *row_prod_ptr = nullptr;
     BSP_TRY(bsp_alloc(ctx, &row_cnt, (size_t)nbr + 1));
     BSP_TRY(bsp_alloc(ctx, &row_prod, (size_t)nbr + 1));
     BSP_TRY(bsp_alloc(ctx, &row_prod_ptr, (size_t)nbr + 1));
     BSP_TRY(bsp_alloc(ctx, &lists, (size_t)NCLASS * (nbr > 0 ? nbr : 1)));
-    BSP_TRY(bsp_alloc(ctx, &counts, (size_t)NCLASS));
+    BSP_TRY(bsp_alloc(ctx, &counts, (size_t)NCLASS + 1)); // [NCLASS] = number of heavy rows of the count pass
+    BSP_TRY(bsp_alloc(ctx, &heavy, (size_t)(nbr > 0 ? nbr : 1)));
     BSP_TRY(bsp_alloc(ctx, &out->c_rowptr, (size_t)nbr + 1));
     BSP_CUDA(ctx, cudaMemsetAsync(row_cnt + nbr, 0, sizeof(int32_t), ctx->stream));
     BSP_CUDA(ctx, cudaMemsetAsync(row_prod + nbr, 0, sizeof(int32_t), ctx->stream));
-    BSP_CUDA(ctx, cudaMemsetAsync(counts, 0, NCLASS * sizeof(int32_t), ctx->stream));
+    BSP_CUDA(ctx, cudaMemsetAsync(counts, 0, (NCLASS + 1) * sizeof(int32_t), ctx->stream));
 
     int grid = (nbr + SYM_WARPS - 1) / SYM_WARPS;
     const int max_grid = ctx->sm_count * 8;
@@ -484,8 +589,17 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)smem_count));
         sym_count_kernel<<<grid, SYM_THREADS, smem_count, ctx->stream>>>(
-            nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, row_lo, row_hi, row_cnt, row_prod);
+            nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, row_lo, row_hi, row_cnt, row_prod, heavy,
+            counts + NCLASS);
         BSP_LAUNCH_CHECK(ctx);
+        {
+            const size_t hb = (size_t)words * sizeof(uint32_t);
+            BSP_CUDA(ctx, cudaFuncSetAttribute(sym_count_heavy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hb));
+            int hgrid = nbr < ctx->sm_count * 4 ? nbr : ctx->sm_count * 4; // CTAs loop over the (device-side) list
+            sym_count_heavy_kernel<<<hgrid, HEAVY_THREADS, hb, ctx->stream>>>(heavy, counts + NCLASS, A->rowptr, A->colidx,
+                                                                              B->nbr, B->rowptr, B->colidx, words, row_cnt);
+            BSP_LAUNCH_CHECK(ctx);
+        }
         classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, A->rowptr, row_cnt, row_prod, caps[0],
                                                                         caps[1], caps[2], tcaps[0], tcaps[1], tcaps[2],
                                                                         acap, lists, counts);
@@ -540,5 +654,6 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     bsp_release(ctx, row_prod_ptr);
     bsp_release(ctx, lists);
     bsp_release(ctx, counts);
+    bsp_release(ctx, heavy);
     return BSP_OK;
 }
