@@ -48,7 +48,7 @@ typedef struct bsp_stats {
     double ms_total;                /* whole call, device time */
     int64_t launches;               /* kernels launched by this call */
     int64_t exact_refolds;          /* output elements recomputed with the per-operation path */
-    int32_t numeric_path;           /* which numeric kernel ran: 0 generic, 4 / 8 / 16 / 32 = tile-size specialised */
+    int32_t numeric_path;           /* numeric kernel that ran: 0 generic exact, 4 / 8 = specialised u64; 100 = fp32 SIMT, 132 / 164 = tensor cores k=32 / 64 */
     int32_t reserved;
 } bsp_stats;
 
@@ -71,6 +71,18 @@ const char *bsp_version(void);
  * reader's m[{row,col}] = v does (cu:383).  Coordinates must be >= 0. */
 int bsp_mat_from_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,
                      const int32_t *brow, const int32_t *bcol, const uint64_t *vals, bsp_mat **out);
+
+/* float32 tiles (BASELINE.json configs[4]; an extension -- the reference reads and multiplies
+ * uint64 only, cu:375-376, cu:44-66, so there is no reference path to match): same pattern
+ * handling, products accumulated in fp32, by tensor cores for k = 32 / 64 (TF32 inputs) or by
+ * an fp32 SIMT kernel.  bsp_spgemm / bsp_chain / bsp_prune_zero / panels work on either type;
+ * both operands must have the same type. */
+int bsp_mat_from_coo_f32(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,
+                         const int32_t *brow, const int32_t *bcol, const float *vals, bsp_mat **out);
+int bsp_mat_to_coo_f32(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol, float *vals);
+int bsp_mat_is_f32(const bsp_mat *m);
+/* float32 products: 0 = auto (tensor cores where a kernel exists), 1 = fp32 SIMT, 2 = tensor cores */
+int bsp_ctx_set_f32_path(bsp_ctx *ctx, int path);
 
 /* Same, from DEVICE memory (arrays are copied, not adopted). */
 int bsp_mat_from_device_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,

@@ -48,6 +48,10 @@ _SIGNATURES = {
     "bsp_ctx_sync": (C.c_int, [_VP]),
     "bsp_ctx_launch_count": (C.c_int64, [_VP]),
     "bsp_mat_from_coo": (C.c_int, [_VP, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP, C.POINTER(_VP)]),
+    "bsp_mat_from_coo_f32": (C.c_int, [_VP, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP, C.POINTER(_VP)]),
+    "bsp_mat_to_coo_f32": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    "bsp_mat_is_f32": (C.c_int, [_VP]),
+    "bsp_ctx_set_f32_path": (C.c_int, [_VP, C.c_int]),
     "bsp_mat_from_device_coo": (C.c_int, [_VP, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP, C.POINTER(_VP)]),
     "bsp_mat_info": (C.c_int, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "bsp_mat_to_coo": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
@@ -128,14 +132,20 @@ class Matrix:
     blocks = property(lambda s: s.info()[3])  # one_matrix::blocks
     nnzb = blocks
 
+    @property
+    def is_f32(self):
+        return bool(self.ctx.lib.bsp_mat_is_f32(self.handle))
+
     def to_coo(self, out=None):
-        """(brow, bcol, vals[nnzb,k,k]) sorted by (brow, bcol). `out` = preallocated triple."""
+        """(brow, bcol, vals[nnzb,k,k]) sorted by (brow, bcol). `out` = preallocated triple.
+        vals are uint64, or float32 for a float matrix."""
         _, _, k, n = self.info()
+        f32 = self.is_f32
         if out is None:
-            out = (np.empty(n, np.int32), np.empty(n, np.int32), np.empty((n, k, k), np.uint64))
+            out = (np.empty(n, np.int32), np.empty(n, np.int32), np.empty((n, k, k), np.float32 if f32 else np.uint64))
         br, bc, v = out
-        self.ctx._ck(self.ctx.lib.bsp_mat_to_coo(self.ctx.handle, self.handle, br.ctypes.data, bc.ctypes.data,
-                                                 v.ctypes.data))
+        fn = self.ctx.lib.bsp_mat_to_coo_f32 if f32 else self.ctx.lib.bsp_mat_to_coo
+        self.ctx._ck(fn(self.ctx.handle, self.handle, br.ctypes.data, bc.ctypes.data, v.ctypes.data))
         return br, bc, v
 
     def device_view(self):
@@ -203,6 +213,21 @@ class Context:
         self._ck(self.lib.bsp_mat_from_coo(self.handle, rows, cols, k, br.size, br.ctypes.data, bc.ctypes.data,
                                            v.ctypes.data, C.byref(h)))
         return Matrix(self, h.value)
+
+    def matrix_from_coo_f32(self, rows, cols, k, brow, bcol, vals):
+        """float32 tiles (extension, BASELINE.json configs[4])."""
+        br, bc = _i32(brow), _i32(bcol)
+        v = np.ascontiguousarray(vals, dtype=np.float32).reshape(-1)
+        if v.size != br.size * k * k or bc.size != br.size:
+            raise ValueError("coordinate list shape mismatch")
+        h = _VP()
+        self._ck(self.lib.bsp_mat_from_coo_f32(self.handle, rows, cols, k, br.size, br.ctypes.data, bc.ctypes.data,
+                                               v.ctypes.data, C.byref(h)))
+        return Matrix(self, h.value)
+
+    def set_f32_path(self, path):
+        """'auto' | 'simt' | 'tensor' for float32 products."""
+        self._ck(self.lib.bsp_ctx_set_f32_path(self.handle, {"auto": 0, "simt": 1, "tensor": 2}[path]))
 
     def matrix_from_device_coo(self, rows, cols, k, nnzb, d_brow, d_bcol, d_vals):
         h = _VP()

@@ -9,11 +9,13 @@ namespace {
 
 bool valid_mat(const bsp_mat *m) { return m && m->rowptr; }
 
-int new_empty_like(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbr, int32_t nbc, bsp_mat **out)
+int new_empty_like(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbr, int32_t nbc, bsp_mat **out,
+                   int32_t esize = 8)
 {
     bsp_mat *m = new (std::nothrow) bsp_mat();
     if (!m) BSP_FAIL(ctx, BSP_ERR_NOMEM, "host allocation failed");
     m->rows = rows; m->cols = cols; m->k = k; m->nbr = nbr; m->nbc = nbc; m->nnzb = 0; m->device = ctx->device;
+    m->esize = esize;
     m->rowptr = nullptr; m->colidx = nullptr; m->vals = nullptr;
     *out = m;
     return BSP_OK;
@@ -34,6 +36,7 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     *C = nullptr;
     if (!valid_mat(A) || !valid_mat(B)) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm: null matrix");
     if (A->k != B->k) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm: tile edge differs (%d vs %d)", A->k, B->k);
+    if (A->esize != B->esize) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm: entry types differ (uint64 vs float32)");
     if (A->device != ctx->device || B->device != ctx->device)
         BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_spgemm: matrices live on another device than the context");
     BSP_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -43,7 +46,7 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     st.nnzb_a = A->nnzb; st.nnzb_b = B->nnzb;
 
     bsp_mat *c = nullptr;
-    BSP_TRY(new_empty_like(ctx, A->rows, B->cols, A->k, A->nbr, B->nbc, &c)); // cu:280-282
+    BSP_TRY(new_empty_like(ctx, A->rows, B->cols, A->k, A->nbr, B->nbc, &c, A->esize)); // cu:280-282
     *C = c;
     BSP_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
     bsp_trace_mark(ctx, "start");
@@ -53,9 +56,10 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     c->rowptr = sym.c_rowptr;
     c->colidx = sym.c_colidx;
     c->nnzb = sym.nnzb_c;
-    BSP_TRY(bsp_alloc(ctx, &c->vals, (size_t)sym.nnzb_c * A->k * A->k));
+    BSP_TRY(bsp_alloc(ctx, (char **)&c->vals, (size_t)sym.nnzb_c * A->k * A->k * A->esize));
     bsp_trace_mark(ctx, "alloc_c");
-    BSP_TRY(bsp_numeric(ctx, A, B, &sym, c->vals, &st.exact_refolds, &st.numeric_path));
+    if (A->esize == 8) BSP_TRY(bsp_numeric(ctx, A, B, &sym, c->vals, &st.exact_refolds, &st.numeric_path));
+    else BSP_TRY(bsp_numeric_f32(ctx, A, B, &sym, (float *)c->vals, &st.numeric_path));
     bsp_trace_mark(ctx, "numeric");
     BSP_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
     bsp_release(ctx, sym.pair_ptr);
@@ -64,7 +68,7 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     float ms01 = 0, ms12 = 0;
     BSP_CUDA(ctx, cudaEventElapsedTime(&ms01, ctx->ev[0], ctx->ev[1]));
     BSP_CUDA(ctx, cudaEventElapsedTime(&ms12, ctx->ev[1], ctx->ev[2]));
-    if (st.numeric_path != 0) st.exact_refolds = (int64_t) * (unsigned long long *)((char *)ctx->pinned + 64);
+    if (st.numeric_path != 0 && A->esize == 8) st.exact_refolds = (int64_t) * (unsigned long long *)((char *)ctx->pinned + 64);
     st.nnzb_c = sym.nnzb_c; st.nprod = sym.nprod;
     st.ms_symbolic = ms01; st.ms_numeric = ms12; st.ms_total = ms01 + ms12;
     st.launches = ctx->launches - launches0;
@@ -76,18 +80,18 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
 int clone_mat(bsp_ctx *ctx, const bsp_mat *s, bsp_mat **out)
 {
     bsp_mat *m = nullptr;
-    BSP_TRY(new_empty_like(ctx, s->rows, s->cols, s->k, s->nbr, s->nbc, &m));
+    BSP_TRY(new_empty_like(ctx, s->rows, s->cols, s->k, s->nbr, s->nbc, &m, s->esize));
     *out = m;
     m->nnzb = s->nnzb;
-    const size_t kk = (size_t)s->k * s->k;
+    const size_t tb = (size_t)s->k * s->k * s->esize; // bytes per tile
     BSP_TRY(bsp_alloc(ctx, &m->rowptr, (size_t)s->nbr + 1));
     BSP_TRY(bsp_alloc(ctx, &m->colidx, (size_t)s->nnzb));
-    BSP_TRY(bsp_alloc(ctx, &m->vals, (size_t)s->nnzb * kk));
+    BSP_TRY(bsp_alloc(ctx, (char **)&m->vals, (size_t)s->nnzb * s->k * s->k * s->esize));
     // cudaMemcpyDefault: the source may live on a peer device (a4 gathers partial products)
     BSP_CUDA(ctx, cudaMemcpyAsync(m->rowptr, s->rowptr, ((size_t)s->nbr + 1) * 4, cudaMemcpyDefault, ctx->stream));
     if (s->nnzb) {
         BSP_CUDA(ctx, cudaMemcpyAsync(m->colidx, s->colidx, (size_t)s->nnzb * 4, cudaMemcpyDefault, ctx->stream));
-        BSP_CUDA(ctx, cudaMemcpyAsync(m->vals, s->vals, (size_t)s->nnzb * kk * 8, cudaMemcpyDefault, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(m->vals, s->vals, (size_t)s->nnzb * tb, cudaMemcpyDefault, ctx->stream));
     }
     return BSP_OK;
 }
@@ -193,11 +197,11 @@ int bsp_mat_from_device_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k,
             if (hc[i] > max_col) max_col = hc[i];
         }
     }
-    return bsp_ingest_coo(ctx, rows, cols, k, nnzb, d_brow, d_bcol, d_vals, max_row, max_col, out);
+    return bsp_ingest_coo(ctx, rows, cols, k, 8, nnzb, d_brow, d_bcol, d_vals, max_row, max_col, out);
 }
 
-int bsp_mat_from_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb, const int32_t *brow,
-                     const int32_t *bcol, const uint64_t *vals, bsp_mat **out)
+static int from_coo_impl(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t esize, int64_t nnzb,
+                         const int32_t *brow, const int32_t *bcol, const void *vals, bsp_mat **out)
 {
     if (!ctx || !out) return BSP_ERR_ARG;
     *out = nullptr;
@@ -211,21 +215,42 @@ int bsp_mat_from_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_
         if (brow[i] > max_row) max_row = brow[i];
         if (bcol[i] > max_col) max_col = bcol[i];
     }
-    const size_t kk = (size_t)k * k;
+    const size_t tb = (size_t)k * k * esize;
     int32_t *d_r = nullptr, *d_c = nullptr;
-    uint64_t *d_v = nullptr;
+    char *d_v = nullptr;
     BSP_TRY(bsp_alloc(ctx, &d_r, (size_t)nnzb));
     BSP_TRY(bsp_alloc(ctx, &d_c, (size_t)nnzb));
-    BSP_TRY(bsp_alloc(ctx, &d_v, (size_t)nnzb * kk));
+    BSP_TRY(bsp_alloc(ctx, &d_v, (size_t)nnzb * tb));
     if (nnzb) {
         BSP_CUDA(ctx, cudaMemcpyAsync(d_r, brow, (size_t)nnzb * 4, cudaMemcpyHostToDevice, ctx->stream));
         BSP_CUDA(ctx, cudaMemcpyAsync(d_c, bcol, (size_t)nnzb * 4, cudaMemcpyHostToDevice, ctx->stream));
-        BSP_CUDA(ctx, cudaMemcpyAsync(d_v, vals, (size_t)nnzb * kk * 8, cudaMemcpyHostToDevice, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(d_v, vals, (size_t)nnzb * tb, cudaMemcpyHostToDevice, ctx->stream));
     }
-    int rc = bsp_ingest_coo(ctx, rows, cols, k, nnzb, d_r, d_c, d_v, max_row, max_col, out);
+    int rc = bsp_ingest_coo(ctx, rows, cols, k, esize, nnzb, d_r, d_c, d_v, max_row, max_col, out);
     bsp_release(ctx, d_r); bsp_release(ctx, d_c); bsp_release(ctx, d_v);
     if (rc == BSP_OK) BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // host buffers may be reused on return
     return rc;
+}
+
+int bsp_mat_from_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb, const int32_t *brow,
+                     const int32_t *bcol, const uint64_t *vals, bsp_mat **out)
+{
+    return from_coo_impl(ctx, rows, cols, k, 8, nnzb, brow, bcol, vals, out);
+}
+
+int bsp_mat_from_coo_f32(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb, const int32_t *brow,
+                         const int32_t *bcol, const float *vals, bsp_mat **out)
+{
+    return from_coo_impl(ctx, rows, cols, k, 4, nnzb, brow, bcol, vals, out);
+}
+
+int bsp_mat_is_f32(const bsp_mat *m) { return m && m->esize == 4; }
+
+int bsp_ctx_set_f32_path(bsp_ctx *ctx, int path)
+{
+    if (!ctx || path < 0 || path > 2) return BSP_ERR_ARG;
+    ctx->f32_path = path;
+    return BSP_OK;
 }
 
 int bsp_mat_info(const bsp_mat *m, int32_t *rows, int32_t *cols, int32_t *k, int64_t *nnzb)
@@ -238,12 +263,13 @@ int bsp_mat_info(const bsp_mat *m, int32_t *rows, int32_t *cols, int32_t *k, int
     return BSP_OK;
 }
 
-int bsp_mat_to_coo(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol, uint64_t *vals)
+static int to_coo_impl(bsp_ctx *ctx, const bsp_mat *m, int32_t esize, int32_t *brow, int32_t *bcol, void *vals)
 {
     if (!ctx || !valid_mat(m)) return BSP_ERR_ARG;
+    if (m->esize != esize) BSP_FAIL(ctx, BSP_ERR_ARG, "matrix holds %s entries", m->esize == 8 ? "uint64" : "float32");
     if (m->nnzb == 0) return BSP_OK;
     BSP_CUDA(ctx, cudaSetDevice(ctx->device));
-    const size_t kk = (size_t)m->k * m->k;
+    const size_t tb = (size_t)m->k * m->k * m->esize;
     if (brow) {
         int32_t *d_brow = nullptr;
         BSP_TRY(bsp_alloc(ctx, &d_brow, (size_t)m->nnzb));
@@ -252,9 +278,19 @@ int bsp_mat_to_coo(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol,
         bsp_release(ctx, d_brow);
     }
     if (bcol) BSP_CUDA(ctx, cudaMemcpyAsync(bcol, m->colidx, (size_t)m->nnzb * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    if (vals) BSP_CUDA(ctx, cudaMemcpyAsync(vals, m->vals, (size_t)m->nnzb * kk * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (vals) BSP_CUDA(ctx, cudaMemcpyAsync(vals, m->vals, (size_t)m->nnzb * tb, cudaMemcpyDeviceToHost, ctx->stream));
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return BSP_OK;
+}
+
+int bsp_mat_to_coo(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol, uint64_t *vals)
+{
+    return to_coo_impl(ctx, m, 8, brow, bcol, vals);
+}
+
+int bsp_mat_to_coo_f32(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol, float *vals)
+{
+    return to_coo_impl(ctx, m, 4, brow, bcol, vals);
 }
 
 int bsp_mat_device_view(const bsp_mat *m, int32_t *nbrows, int32_t *nbcols, const int32_t **d_rowptr,
@@ -273,13 +309,13 @@ int bsp_mat_export_device(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_rowptr, int
 {
     if (!ctx || !valid_mat(m)) return BSP_ERR_ARG;
     BSP_CUDA(ctx, cudaSetDevice(ctx->device));
-    const size_t kk = (size_t)m->k * m->k;
+    const size_t tb = (size_t)m->k * m->k * m->esize;
     if (d_rowptr)
         BSP_CUDA(ctx, cudaMemcpyAsync(d_rowptr, m->rowptr, ((size_t)m->nbr + 1) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
     if (d_colidx && m->nnzb)
         BSP_CUDA(ctx, cudaMemcpyAsync(d_colidx, m->colidx, (size_t)m->nnzb * 4, cudaMemcpyDeviceToDevice, ctx->stream));
     if (d_vals && m->nnzb)
-        BSP_CUDA(ctx, cudaMemcpyAsync(d_vals, m->vals, (size_t)m->nnzb * kk * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(d_vals, m->vals, (size_t)m->nnzb * tb, cudaMemcpyDeviceToDevice, ctx->stream));
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return BSP_OK;
 }
@@ -293,18 +329,18 @@ int bsp_mat_copy_to_ctx(bsp_ctx *src_ctx, const bsp_mat *m, bsp_ctx *dst_ctx, bs
     BSP_CUDA(src_ctx, cudaStreamSynchronize(src_ctx->stream)); // the source must be complete
     BSP_CUDA(dst_ctx, cudaSetDevice(dst_ctx->device));
     bsp_mat *c = nullptr;
-    BSP_TRY(new_empty_like(dst_ctx, m->rows, m->cols, m->k, m->nbr, m->nbc, &c));
+    BSP_TRY(new_empty_like(dst_ctx, m->rows, m->cols, m->k, m->nbr, m->nbc, &c, m->esize));
     *out = c;
     c->nnzb = m->nnzb;
-    const size_t kk = (size_t)m->k * m->k;
+    const size_t tb = (size_t)m->k * m->k * m->esize;
     BSP_TRY(bsp_alloc(dst_ctx, &c->rowptr, (size_t)m->nbr + 1));
     BSP_TRY(bsp_alloc(dst_ctx, &c->colidx, (size_t)m->nnzb));
-    BSP_TRY(bsp_alloc(dst_ctx, &c->vals, (size_t)m->nnzb * kk));
+    BSP_TRY(bsp_alloc(dst_ctx, (char **)&c->vals, (size_t)m->nnzb * tb));
     const int sd = m->device, dd = dst_ctx->device;
     BSP_CUDA(dst_ctx, cudaMemcpyPeerAsync(c->rowptr, dd, m->rowptr, sd, ((size_t)m->nbr + 1) * 4, dst_ctx->stream));
     if (m->nnzb) {
         BSP_CUDA(dst_ctx, cudaMemcpyPeerAsync(c->colidx, dd, m->colidx, sd, (size_t)m->nnzb * 4, dst_ctx->stream));
-        BSP_CUDA(dst_ctx, cudaMemcpyPeerAsync(c->vals, dd, m->vals, sd, (size_t)m->nnzb * kk * 8, dst_ctx->stream));
+        BSP_CUDA(dst_ctx, cudaMemcpyPeerAsync(c->vals, dd, m->vals, sd, (size_t)m->nnzb * tb, dst_ctx->stream));
     }
     BSP_CUDA(dst_ctx, cudaStreamSynchronize(dst_ctx->stream));
     return BSP_OK;
@@ -325,6 +361,7 @@ int bsp_mat_from_device_bcsr(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k
     tmp.colidx = const_cast<int32_t *>(d_colidx);
     tmp.vals = const_cast<uint64_t *>(d_vals);
     tmp.device = ctx->device;
+    tmp.esize = 8;
     return clone_mat(ctx, &tmp, out);
 }
 
@@ -360,7 +397,7 @@ int bsp_mat_concat_panels(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_m
     int64_t total = 0;
     for (int i = 0; i < n; i++) {
         if (!valid_mat(panels[i])) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_concat_panels: panel %d is null", i);
-        if (panels[i]->k != panels[0]->k || panels[i]->nbr != panels[0]->nbr)
+        if (panels[i]->k != panels[0]->k || panels[i]->nbr != panels[0]->nbr || panels[i]->esize != panels[0]->esize)
             BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_concat_panels: panel %d has another shape", i);
         total += panels[i]->nnzb;
     }
@@ -369,12 +406,12 @@ int bsp_mat_concat_panels(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_m
     bsp_mat *m = nullptr;
     int32_t nbc = 0;
     for (int i = 0; i < n; i++) nbc = panels[i]->nbc > nbc ? panels[i]->nbc : nbc;
-    BSP_TRY(new_empty_like(ctx, panels[0]->rows, panels[0]->cols, panels[0]->k, panels[0]->nbr, nbc, &m));
+    BSP_TRY(new_empty_like(ctx, panels[0]->rows, panels[0]->cols, panels[0]->k, panels[0]->nbr, nbc, &m, panels[0]->esize));
     *out = m;
     m->nnzb = total;
     BSP_TRY(bsp_alloc(ctx, &m->rowptr, (size_t)m->nbr + 1));
     BSP_TRY(bsp_alloc(ctx, &m->colidx, (size_t)total));
-    BSP_TRY(bsp_alloc(ctx, &m->vals, (size_t)total * m->k * m->k));
+    BSP_TRY(bsp_alloc(ctx, (char **)&m->vals, (size_t)total * m->k * m->k * m->esize));
     return bsp_concat_panels_device(ctx, panels, n, m);
 }
 

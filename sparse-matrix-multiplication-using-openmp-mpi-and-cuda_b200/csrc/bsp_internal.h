@@ -27,6 +27,7 @@ struct bsp_ctx {
     size_t pinned_bytes;
     void *d_counters;    // 256 B of device counters (exact-refold count of the numeric pass)
     bool force_generic;  // BSP_FORCE_GENERIC=1: always use the any-k exact numeric kernel (tests)
+    int f32_path;        // float32 products: 0 = auto (tensor cores for k = 32 / 64), 1 = SIMT, 2 = tensor cores
     bool trace;          // BSP_TRACE=1: per-sub-phase device timings of every product on stderr
     int ntrace;
     cudaEvent_t trace_ev[32];
@@ -40,8 +41,9 @@ struct bsp_mat {
     int64_t nnzb;
     int32_t *rowptr;     // device
     int32_t *colidx;     // device
-    uint64_t *vals;      // device
+    uint64_t *vals;      // device; raw tile storage (uint64 entries, or float32 entries when esize == 4)
     int device;
+    int32_t esize;       // bytes per entry: 8 = uint64 (the reference's type), 4 = float32 (extension)
 };
 
 #define BSP_FAIL(ctx, code, ...)                                  \
@@ -141,6 +143,9 @@ int bsp_numeric(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
 int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m);
 int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_mat *out);
 int bsp_expand_rows(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_brow);
-int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,
-                   const int32_t *d_brow, const int32_t *d_bcol, const uint64_t *d_vals,
+int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t esize, int64_t nnzb,
+                   const int32_t *d_brow, const int32_t *d_bcol, const void *d_vals,
                    int32_t max_row, int32_t max_col, bsp_mat **out);
+// float32 numeric pass (extension; no reference counterpart)
+int bsp_numeric_f32(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym, float *c_vals,
+                    int32_t *path);

@@ -53,9 +53,10 @@ __global__ void scatter_index_kernel(const uint64_t *__restrict__ keys, const in
 }
 
 // gather tiles: one CTA-strided loop over (tile, 16-byte chunk)
-__global__ void gather_tiles_kernel(const uint64_t *__restrict__ src, const int32_t *__restrict__ idx,
+// (tiles are moved as 32-bit words so that the same kernels serve uint64 and float32 entries)
+__global__ void gather_tiles_kernel(const uint32_t *__restrict__ src, const int32_t *__restrict__ idx,
                                     const int32_t *__restrict__ keep, const int32_t *__restrict__ pos, int64_t n,
-                                    int kk, uint64_t *__restrict__ dst)
+                                    int kk, uint32_t *__restrict__ dst)
 {
     const int64_t total = n * kk;
     for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
@@ -79,14 +80,14 @@ __global__ void expand_rows_kernel(const int32_t *__restrict__ rowptr, int32_t n
 }
 
 // one warp per tile: keep = any entry non-zero (cu:580-586)
-__global__ void tile_nonzero_kernel(const uint64_t *__restrict__ vals, int64_t nnzb, int kk, int32_t *__restrict__ keep)
+__global__ void tile_nonzero_kernel(const uint32_t *__restrict__ vals, int64_t nnzb, int kk, int32_t *__restrict__ keep)
 {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t t = warp; t < nnzb; t += nwarps) {
-        const uint64_t *v = vals + (size_t)t * kk;
-        uint64_t acc = 0;
+        const uint32_t *v = vals + (size_t)t * kk;
+        uint32_t acc = 0;
         for (int e = lane; e < kk; e += 32) acc |= v[e];
         const unsigned any = __ballot_sync(0xffffffffu, acc != 0);
         if (lane == 0) keep[t] = any ? 1 : 0;
@@ -94,9 +95,9 @@ __global__ void tile_nonzero_kernel(const uint64_t *__restrict__ vals, int64_t n
     if (warp == 0 && lane == 0) keep[nnzb] = 0;
 }
 
-__global__ void compact_tiles_kernel(const uint64_t *__restrict__ vals, const int32_t *__restrict__ colidx,
+__global__ void compact_tiles_kernel(const uint32_t *__restrict__ vals, const int32_t *__restrict__ colidx,
                                      const int32_t *__restrict__ keep, const int32_t *__restrict__ pos, int64_t nnzb,
-                                     int kk, uint64_t *__restrict__ vals_out, int32_t *__restrict__ colidx_out)
+                                     int kk, uint32_t *__restrict__ vals_out, int32_t *__restrict__ colidx_out)
 {
     const int64_t total = nnzb * kk;
     for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int64_t)gridDim.x * blockDim.x) {
@@ -126,16 +127,17 @@ inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)((n + thre
 
 } // namespace
 
-int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb, const int32_t *d_brow,
-                   const int32_t *d_bcol, const uint64_t *d_vals, int32_t max_row, int32_t max_col, bsp_mat **out)
+int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t esize, int64_t nnzb,
+                   const int32_t *d_brow, const int32_t *d_bcol, const void *d_vals, int32_t max_row, int32_t max_col,
+                   bsp_mat **out)
 {
     bsp_mat *m = new bsp_mat();
-    m->rows = rows; m->cols = cols; m->k = k; m->device = ctx->device;
+    m->rows = rows; m->cols = cols; m->k = k; m->device = ctx->device; m->esize = esize;
     m->nbr = nnzb > 0 ? max_row + 1 : 0;
     m->nbc = nnzb > 0 ? max_col + 1 : 0;
     m->nnzb = 0; m->rowptr = nullptr; m->colidx = nullptr; m->vals = nullptr;
     *out = m;
-    const int kk = k * k;
+    const int kk = k * k * (esize / 4); // 32-bit words per tile
     BSP_TRY(bsp_alloc(ctx, &m->rowptr, (size_t)m->nbr + 1));
     if (nnzb == 0) {
         BSP_CUDA(ctx, cudaMemsetAsync(m->rowptr, 0, sizeof(int32_t), ctx->stream));
@@ -167,7 +169,7 @@ int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t 
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     m->nnzb = *h_uniq;
     BSP_TRY(bsp_alloc(ctx, &m->colidx, (size_t)m->nnzb));
-    BSP_TRY(bsp_alloc(ctx, &m->vals, (size_t)m->nnzb * kk));
+    BSP_TRY(bsp_alloc(ctx, (uint32_t **)&m->vals, (size_t)m->nnzb * kk));
     scatter_index_kernel<<<blocks_for(nnzb, 256), 256, 0, ctx->stream>>>(keys2, keep, pos, nnzb, m->nbr, m->rowptr,
                                                                          m->colidx);
     BSP_LAUNCH_CHECK(ctx);
@@ -175,7 +177,8 @@ int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t 
         int64_t total = nnzb * kk;
         int64_t g = (total + 255) / 256;
         if (g > (int64_t)ctx->sm_count * 32) g = (int64_t)ctx->sm_count * 32;
-        gather_tiles_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>(d_vals, idx2, keep, pos, nnzb, kk, m->vals);
+        gather_tiles_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>((const uint32_t *)d_vals, idx2, keep, pos, nnzb, kk,
+                                                                  (uint32_t *)m->vals);
         BSP_LAUNCH_CHECK(ctx);
     }
     bsp_release(ctx, keys); bsp_release(ctx, keys2); bsp_release(ctx, idx); bsp_release(ctx, idx2);
@@ -194,14 +197,14 @@ int bsp_expand_rows(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_brow)
 int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m)
 {
     if (m->nnzb == 0) return BSP_OK;
-    const int kk = m->k * m->k;
+    const int kk = m->k * m->k * (m->esize / 4); // 32-bit words per tile
     int32_t *keep = nullptr, *pos = nullptr;
     BSP_TRY(bsp_alloc(ctx, &keep, (size_t)m->nnzb + 1));
     BSP_TRY(bsp_alloc(ctx, &pos, (size_t)m->nnzb + 1));
     {
         int64_t g = (m->nnzb * 32 + 255) / 256;
         if (g > (int64_t)ctx->sm_count * 16) g = (int64_t)ctx->sm_count * 16;
-        tile_nonzero_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>(m->vals, m->nnzb, kk, keep);
+        tile_nonzero_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>((const uint32_t *)m->vals, m->nnzb, kk, keep);
         BSP_LAUNCH_CHECK(ctx);
     }
     BSP_TRY(bsp_scan_i32(ctx, keep, pos, m->nnzb + 1, nullptr));
@@ -211,21 +214,21 @@ int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m)
     const int64_t kept = *h_kept;
     if (kept != m->nnzb) {
         int32_t *rowptr2 = nullptr, *colidx2 = nullptr;
-        uint64_t *vals2 = nullptr;
+        uint32_t *vals2 = nullptr;
         BSP_TRY(bsp_alloc(ctx, &rowptr2, (size_t)m->nbr + 1));
         BSP_TRY(bsp_alloc(ctx, &colidx2, (size_t)kept));
         BSP_TRY(bsp_alloc(ctx, &vals2, (size_t)kept * kk));
         int64_t total = m->nnzb * kk;
         int64_t g = (total + 255) / 256;
         if (g > (int64_t)ctx->sm_count * 32) g = (int64_t)ctx->sm_count * 32;
-        compact_tiles_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>(m->vals, m->colidx, keep, pos, m->nnzb, kk, vals2,
-                                                                    colidx2);
+        compact_tiles_kernel<<<(unsigned)g, 256, 0, ctx->stream>>>((const uint32_t *)m->vals, m->colidx, keep, pos,
+                                                                    m->nnzb, kk, vals2, colidx2);
         BSP_LAUNCH_CHECK(ctx);
         remap_rowptr_kernel<<<blocks_for((int64_t)m->nbr + 1, 256), 256, 0, ctx->stream>>>(m->rowptr, m->nbr, pos,
                                                                                             rowptr2);
         BSP_LAUNCH_CHECK(ctx);
         bsp_release(ctx, m->rowptr); bsp_release(ctx, m->colidx); bsp_release(ctx, m->vals);
-        m->rowptr = rowptr2; m->colidx = colidx2; m->vals = vals2; m->nnzb = kept;
+        m->rowptr = rowptr2; m->colidx = colidx2; m->vals = (uint64_t *)vals2; m->nnzb = kept;
     }
     bsp_release(ctx, keep);
     bsp_release(ctx, pos);
@@ -238,7 +241,7 @@ int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bs
     // nnzb_i after it: the row pointers of the concatenation are the element-wise sum, and
     // colidx / vals are the panels' arrays back to back.
     const int nbr = out->nbr;
-    const size_t kk = (size_t)out->k * out->k;
+    const size_t tb = (size_t)out->k * out->k * out->esize; // bytes per tile
     BSP_CUDA(ctx, cudaMemsetAsync(out->rowptr, 0, ((size_t)nbr + 1) * sizeof(int32_t), ctx->stream));
     int64_t off = 0;
     for (int i = 0; i < n; i++) {
@@ -247,7 +250,7 @@ int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bs
         BSP_LAUNCH_CHECK(ctx);
         if (p->nnzb) {
             BSP_CUDA(ctx, cudaMemcpyAsync(out->colidx + off, p->colidx, (size_t)p->nnzb * 4, cudaMemcpyDefault, ctx->stream));
-            BSP_CUDA(ctx, cudaMemcpyAsync(out->vals + (size_t)off * kk, p->vals, (size_t)p->nnzb * kk * 8, cudaMemcpyDefault, ctx->stream));
+            BSP_CUDA(ctx, cudaMemcpyAsync((char *)out->vals + (size_t)off * tb, p->vals, (size_t)p->nnzb * tb, cudaMemcpyDefault, ctx->stream));
         }
         off += p->nnzb;
     }

@@ -90,6 +90,7 @@ extern "C" int bsp_mat_read_text(bsp_ctx *ctx, const char *path, int32_t k, bsp_
 extern "C" int bsp_mat_write_text(bsp_ctx *ctx, const bsp_mat *m, const char *path)
 {
     if (!ctx || !m || !path) return BSP_ERR_ARG;
+    if (m->esize != 8) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_write_text: the reference's text format holds uint64 entries only");
     int32_t rows, cols, k;
     int64_t nnzb;
     bsp_mat_info(m, &rows, &cols, &k, &nnzb);
