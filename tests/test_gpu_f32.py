@@ -84,3 +84,12 @@ def test_mixed_types_rejected(ctx):
     U = ctx.matrix_from_coo(16, 16, 4, a[3], a[4], np.ones(a[3].size * 16, np.uint64))
     with pytest.raises(bspgemm.BspError):
         ctx.helper(A, U)
+
+
+@pytest.mark.parametrize("k", [32, 64])
+def test_f32_tensor_cores_match_float64_within_tf32(ctx, k):
+    st = check(ctx, k, 9, 0.35, "tensor", 2e-3, seeds=(7, 8))
+    assert st.numeric_path == 100 + k
+    # auto picks the tensor-core kernel for these tile sizes
+    st = check(ctx, k, 6, 0.5, "auto", 2e-3, seeds=(9, 10))
+    assert st.numeric_path == 100 + k
