@@ -350,6 +350,62 @@ def run_rmat(torch, dist, ctx, rank, world, steps):
 
 
 # --------------------------------------------------------------------------------------------
+# secondary figure: float32 tiles, tensor cores vs SIMT (BASELINE.json configs[4])
+# --------------------------------------------------------------------------------------------
+
+def run_float(torch, ctx, k, n, density, steps):
+    """float32 tiles of edge k, block density `density`, values U(-1,1).  The reference has no
+    float path; the checker is a float64 evaluation of sampled output tiles.  Reports both numeric
+    kernels (tcgen05 TF32 and fp32 SIMT) and their worst error relative to sum|a||b|."""
+    import bsp_gen
+    import bspgemm
+    G = n // k
+    mats = []
+    for seed in (21, 22):
+        br, bc = bsp_gen.bernoulli_pattern(G, G, density, seed)
+        u = bsp_gen.splitmix64(seed ^ 0xABCDEF, br.size * k * k).astype(np.float64) / 2.0 ** 64
+        mats.append((n, n, k, br, bc, (2.0 * u - 1.0).astype(np.float32).reshape(-1, k, k)))
+    A, B = ctx.matrix_from_coo_f32(*mats[0]), ctx.matrix_from_coo_f32(*mats[1])
+    out = {"workload": "float32 tiles k=%d, n=%d, %.3g%% block density, U(-1,1) entries" % (k, n, density * 100)}
+    a, b = mats
+    a_key = a[3].astype(np.int64) * G + a[4]
+    b_key = b[3].astype(np.int64) * G + b[4]
+    for path in ("tensor", "simt"):
+        ctx.set_f32_path(path)
+        st = bspgemm.Stats()
+        ms = []
+        for i in range(steps + 2):
+            C = ctx.helper(A, B, stats=st)
+            if i >= 2:
+                ms.append(st.ms_numeric)
+            if i < steps + 1:
+                C.free()
+        br, bc, v = C.to_coo()
+        rng = np.random.default_rng(5)
+        worst = 0.0
+        for t in rng.integers(0, br.size, 24):
+            i, c = int(br[t]), int(bc[t])
+            js = a[4][np.searchsorted(a[3], i):np.searchsorted(a[3], i + 1)]
+            ref = np.zeros((k, k)); bound = np.zeros((k, k))
+            for j in js:
+                q = np.searchsorted(b_key, int(j) * G + c)
+                if q < b_key.size and b_key[q] == int(j) * G + c:
+                    At = a[5][np.searchsorted(a_key, i * G + int(j))].astype(np.float64)
+                    Bt = b[5][q].astype(np.float64)
+                    ref += At @ Bt; bound += np.abs(At) @ np.abs(Bt)
+            worst = max(worst, float((np.abs(v[t] - ref) / np.maximum(bound, 1e-30)).max()))
+        C.free()
+        t_ms = sum(ms) / len(ms)
+        out[path] = {"numeric_ms": t_ms, "numeric_path": st.numeric_path, "gflops": 2.0 * k ** 3 * st.nprod / (t_ms * 1e-3) / 1e9,
+                     "max_err_over_sum_abs": worst}
+        out["nprod"], out["nnzb_c"], out["symbolic_ms"] = st.nprod, st.nnzb_c, st.ms_symbolic
+    ctx.set_f32_path("auto")
+    out["tolerance"] = "tensor (TF32 inputs, fp32 accumulate) <= 2e-3, simt (fp32 FMA) <= 2e-6, relative to sum_j |a_j||b_j|"
+    A.free(); B.free()
+    return out
+
+
+# --------------------------------------------------------------------------------------------
 # our arm
 # --------------------------------------------------------------------------------------------
 
@@ -366,6 +422,7 @@ def main():
     ap.add_argument("--no-chain", action="store_true")
     ap.add_argument("--rmat", action="store_true", help="also run the R-MAT row-panel figure (default: only when --gpus > 1)")
     ap.add_argument("--no-rmat", action="store_true")
+    ap.add_argument("--no-float", action="store_true")
     ap.add_argument("--chain-steps", type=int, default=2)
     args = ap.parse_args()
     if args.impl == "reference":
@@ -490,6 +547,10 @@ def main():
         if (args.rmat or world > 1) and not args.no_rmat:
             rmat = run_rmat(torch, dist, ctx, rank, world, 3)
 
+        floats = None
+        if world == 1 and not args.no_float:
+            floats = [run_float(torch, ctx, 32, 65536, 0.02, 3), run_float(torch, ctx, 64, 65536, 0.02, 3)]
+
         if rank == 0:
             peak, peak_src = measured_peak()
             alg = algorithmic_bytes(st.nnzb_a, st.nnzb_b, st.nnzb_c, G, k)
@@ -523,6 +584,8 @@ def main():
                 line["chain"] = chain
             if rmat:
                 line["rmat_panels"] = rmat
+            if floats:
+                line["float32_tiles"] = floats
             if world == 1 and not args.no_cpu:
                 try:
                     cb = cpu_reference_measure(n, k, d, steps=1, warmup=0)

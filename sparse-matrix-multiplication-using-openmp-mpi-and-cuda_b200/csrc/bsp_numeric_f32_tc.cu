@@ -208,8 +208,9 @@ int bsp_numeric_f32_tc(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const b
         return BSP_ERR_LIMIT;
     }
     const float *a = (const float *)A->vals, *b = (const float *)B->vals;
+    // latency-bound per CTA (load -> MMA -> load ...): fill the SM with as many CTAs as shared memory allows
     int64_t grid = sym->nnzb_c;
-    const int64_t max_grid = (int64_t)ctx->sm_count * 4;
+    const int64_t max_grid = (int64_t)ctx->sm_count * (k == 32 ? 8 : 3);
     if (grid > max_grid) grid = max_grid;
     if (k == 32) {
         constexpr int smem = 2 * ((32 / 4) * 64 * 16 + (32 / 4) * 32 * 16);
