@@ -90,6 +90,6 @@ def test_mixed_types_rejected(ctx):
 def test_f32_tensor_cores_match_float64_within_tf32(ctx, k):
     st = check(ctx, k, 9, 0.35, "tensor", 2e-3, seeds=(7, 8))
     assert st.numeric_path == 100 + k
-    # auto picks the tensor-core kernel for these tile sizes
+    # auto picks the tensor-core kernel where it is the faster one (k = 64)
     st = check(ctx, k, 6, 0.5, "auto", 2e-3, seeds=(9, 10))
-    assert st.numeric_path == 100 + k
+    assert st.numeric_path == (164 if k == 64 else 100)
