@@ -3,7 +3,7 @@
 // Reader: "rows cols", "blocks", then per block "brow bcol" and k*k whitespace-separated
 // uint64 values (cu:345-383).  The reference parses with ifstream >> (one task per file on
 // 16 OpenMP threads, cu:334-339); here a file is read whole and parsed with a hand-rolled
-// decimal scanner, optionally split across threads at block boundaries.
+// decimal scanner, split across host threads at token boundaries (two passes: count, parse).
 // Writer: cu:595-608 -- "R C", block count, then per tile (in (brow,bcol) order) "i j" and k
 // lines of k values separated by single spaces, no trailing space, '\n' line ends.
 #include <charconv>
@@ -77,12 +77,65 @@ extern "C" int bsp_mat_read_text(bsp_ctx *ctx, const char *path, int32_t k, bsp_
     const size_t kk = (size_t)k * k;
     std::vector<int32_t> br((size_t)blocks), bc((size_t)blocks);
     std::vector<uint64_t> v((size_t)blocks * kk);
-    for (int32_t b = 0; b < blocks && ok; b++) {
-        p = parse_i32(p, e, &br[b], &ok);
-        p = parse_i32(p, e, &bc[b], &ok);
-        uint64_t *t = v.data() + (size_t)b * kk;
-        for (size_t i = 0; i < kk; i++) p = parse_u64(p, e, &t[i], &ok);
+    // The body is blocks * (2 + k*k) whitespace-separated tokens.  Parse it on several threads:
+    // cut the text at whitespace, count the tokens of every piece, prefix-sum the counts so each
+    // piece knows the global number of its first token, then parse the pieces independently
+    // (token g belongs to block g / (2+k*k), field g % (2+k*k)).
+    const size_t per_block = 2 + kk;
+    const size_t want_tokens = (size_t)blocks * per_block;
+    unsigned nt = std::thread::hardware_concurrency();
+    if (nt < 1) nt = 1;
+    if (nt > 32) nt = 32;
+    const size_t body = (size_t)(e - p);
+    if (body < (1u << 20)) nt = 1;
+    std::vector<const char *> cut(nt + 1);
+    cut[0] = p; cut[nt] = e;
+    for (unsigned i = 1; i < nt; i++) {
+        const char *c = p + body * i / nt;
+        while (c < e && (unsigned char)*c > ' ') c++; // move to the end of the token we landed in
+        cut[i] = c;
     }
+    std::vector<size_t> ntok(nt + 1, 0);
+    auto count = [&](unsigned i) {
+        size_t n = 0;
+        const char *c = cut[i], *ce = cut[i + 1];
+        while (c < ce) {
+            while (c < ce && (unsigned char)*c <= ' ') c++;
+            if (c < ce) { n++; while (c < ce && (unsigned char)*c > ' ') c++; }
+        }
+        ntok[i + 1] = n;
+    };
+    auto run_all = [&](auto fn) {
+        if (nt == 1) { fn(0u); return; }
+        std::vector<std::thread> th;
+        for (unsigned i = 0; i < nt; i++) th.emplace_back(fn, i);
+        for (auto &t : th) t.join();
+    };
+    run_all(count);
+    for (unsigned i = 0; i < nt; i++) ntok[i + 1] += ntok[i];
+    if (ntok[nt] < want_tokens) BSP_FAIL(ctx, BSP_ERR_IO, "%s: truncated block list (%zu of %zu values)", path, ntok[nt], want_tokens);
+    std::vector<char> bad(nt, 0);
+    auto parse = [&](unsigned i) {
+        const char *c = cut[i], *ce = cut[i + 1];
+        size_t g = ntok[i];
+        bool okk = true;
+        while (g < want_tokens) {
+            c = skip_ws(c, ce);
+            if (c >= ce) break;
+            const size_t b = g / per_block, f = g - b * per_block;
+            if (f < 2) {
+                int32_t x;
+                c = parse_i32(c, ce, &x, &okk);
+                (f == 0 ? br : bc)[b] = x;
+            } else {
+                c = parse_u64(c, ce, &v[b * kk + (f - 2)], &okk);
+            }
+            if (!okk) { bad[i] = 1; return; }
+            g++;
+        }
+    };
+    run_all(parse);
+    for (unsigned i = 0; i < nt; i++) ok = ok && !bad[i];
     if (!ok) BSP_FAIL(ctx, BSP_ERR_IO, "%s: truncated or malformed block list", path);
     return bsp_mat_from_coo(ctx, rows, cols, k, blocks, br.data(), bc.data(), v.data(), out);
 }

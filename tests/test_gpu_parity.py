@@ -327,3 +327,28 @@ def test_concat_panels(ctx):
     got = ctx.concat_panels(parts).to_coo()
     for x, y in zip(got, full):
         assert np.array_equal(x, y)
+
+
+def test_text_io_roundtrip_large(ctx):
+    """Files above 1 MB are parsed on several host threads; the writer formats in parallel."""
+    k = 8
+    a = bsp_gen.random_matrix(400 * k, 400 * k, k, 0.05, 123, "u64")   # ~8000 tiles, ~10 MB of text
+    A = dev(ctx, a)
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "matrix1")
+        A.write_text(p)
+        assert os.path.getsize(p) > (1 << 20)
+        ref = orc.OMat.from_coo(*a)
+        q = os.path.join(d, "ref")
+        ref.write(q)
+        assert open(p, "rb").read() == open(q, "rb").read()
+        back = ctx.read_text(p, k)
+        assert_same(back, ref)
+        # truncated file -> error code, not a crash
+        with open(p, "rb") as f:
+            data = f.read()
+        with open(p, "wb") as f:
+            f.write(data[: len(data) // 2])
+        with pytest.raises(bspgemm.BspError) as e:
+            ctx.read_text(p, k)
+        assert e.value.code == 5
