@@ -236,7 +236,7 @@ __device__ __forceinline__ ulonglong2 lds128(unsigned smem_addr)
 }
 
 template <int K, int STAGES, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, (WARPS == 4 && K == 4) ? 3 : 1)
 numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restrict__ b_vals,
                     const int64_t *__restrict__ pair_ptr, const int2 *__restrict__ pairs,
                     const int2 *__restrict__ chunk_tiles, const int32_t *__restrict__ nchunks_ptr,
@@ -361,15 +361,25 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
                 }
             }
             const unsigned bsm = st + Cfg::TILE_BYTES;
+            // B row j+1 is fetched from shared memory while row j is being multiplied
+            ulonglong2 bnext[K / 2];
+#pragma unroll
+            for (int c2 = 0; c2 < K / 2; c2++) bnext[c2] = lds128(bsm + c2 * 16);
 #pragma unroll
             for (int j = 0; j < K; j++) {
+                ulonglong2 bcur[K / 2];
+#pragma unroll
+                for (int c2 = 0; c2 < K / 2; c2++) bcur[c2] = bnext[c2];
+                if (j + 1 < K) {
+#pragma unroll
+                    for (int c2 = 0; c2 < K / 2; c2++) bnext[c2] = lds128(bsm + ((j + 1) * (K / 2) + c2) * 16);
+                }
 #pragma unroll
                 for (int c2 = 0; c2 < K / 2; c2++) {
-                    const ulonglong2 bv = lds128(bsm + (j * (K / 2) + c2) * 16); // broadcast inside the group
 #pragma unroll
                     for (int rr = 0; rr < RPT; rr++) {
-                        mac_flag(acc[rr][2 * c2], flag, a_cur[rr][j], bv.x);
-                        mac_flag(acc[rr][2 * c2 + 1], flag, a_cur[rr][j], bv.y);
+                        mac_flag(acc[rr][2 * c2], flag, a_cur[rr][j], bcur[c2].x);
+                        mac_flag(acc[rr][2 * c2 + 1], flag, a_cur[rr][j], bcur[c2].y);
                     }
                 }
             }

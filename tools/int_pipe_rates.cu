@@ -22,6 +22,14 @@ __global__ void __launch_bounds__(256) k(uint32_t *out, int iters, uint32_t seed
                 if (MODE == 3) a[i] = max(a[i] - b[i], a[i]) + 1;                     // VIADDMNMX (+1 add)
                 if (MODE == 4) { a[i] = a[i] * m + n; b[i] = b[i] + a[i] + n; }       // IMAD + IADD3
                 if (MODE == 5) { w[i] = (uint64_t)(uint32_t)w[i] * m + w[i]; b[i] = b[i] + (uint32_t)w[i] + n; } // WIDE + IADD3
+                if (MODE == 7) { const uint64_t t = (uint64_t)a[i] * m; a[i] = (uint32_t)t ^ (uint32_t)(t >> 32); }  // IMAD.WIDE (no addend) + LOP3
+                if (MODE == 8) { uint32_t lo = (uint32_t)w[i], hi = (uint32_t)(w[i] >> 32), tl, th;                // WIDE (no addend) + add.cc/addc + 2 IMAD
+                                 asm("mul.wide.u32 %0, %1, %2;" : "=l"(w[i]) : "r"(a[i]), "r"(m));
+                                 tl = (uint32_t)w[i]; th = (uint32_t)(w[i] >> 32);
+                                 asm("add.cc.u32 %0, %0, %2; addc.u32 %1, %1, %3;" : "+r"(lo), "+r"(hi) : "r"(tl), "r"(th));
+                                 hi = a[i] * n + hi; hi = b[i] * m + hi; a[i] = lo; b[i] = hi; }
+                if (MODE == 9) { w[i] = (uint64_t)a[i] * m + w[i]; uint32_t hi = (uint32_t)(w[i] >> 32);                // WIDE accumulate + 2 IMAD on hi
+                                 hi = a[i] * n + hi; hi = b[i] * m + hi; w[i] = ((uint64_t)hi << 32) | (uint32_t)w[i]; a[i] += 1; }
                 if (MODE == 6) { w[i] = (uint64_t)(uint32_t)w[i] * m + w[i]; a[i] = a[i] * m + n; b[i] = b[i] * n + m; } // WIDE + 2 IMAD
             }
     }
@@ -53,5 +61,8 @@ int main()
     run<4>("IMAD + IADD3", 2, out, p.multiProcessorCount, clk);
     run<5>("IMAD.WIDE + IADD3", 2, out, p.multiProcessorCount, clk);
     run<6>("IMAD.WIDE + 2 IMAD", 3, out, p.multiProcessorCount, clk);
+    run<7>("IMAD.WIDE (no addend) + LOP3", 2, out, p.multiProcessorCount, clk);
+    run<8>("MAC: WIDE(no addend) + add.cc/addc + 2 IMAD  [count as 1]", 1, out, p.multiProcessorCount, clk);
+    run<9>("MAC: WIDE accumulate + 2 IMAD  [count as 1]", 1, out, p.multiProcessorCount, clk);
     return 0;
 }
