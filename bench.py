@@ -34,6 +34,8 @@ WORKLOADS = {
     "cfg2": (65536, 8, 0.01, "u64"),
     "cfg1": (1024, 4, 0.05, "u64"),
     "mid": (16384, 8, 0.01, "u64"),
+    "k16": (65536, 16, 0.02, "u64"),
+    "k32": (65536, 32, 0.02, "u64"),   # the tile size of the reference's own published numbers (report.pdf)
 }
 # DRAM bytes of one numeric-kernel launch from the committed `ncu --set full` capture (not measured live)
 NCU_TRAFFIC_BYTES = {("cfg2", 8): 30182856000 + 19197000000}

@@ -48,7 +48,7 @@ typedef struct bsp_stats {
     double ms_total;                /* whole call, device time */
     int64_t launches;               /* kernels launched by this call */
     int64_t exact_refolds;          /* output elements recomputed with the per-operation path */
-    int32_t numeric_path;           /* numeric kernel that ran: 0 generic exact, 4 / 8 = specialised u64; 100 = fp32 SIMT, 132 / 164 = tensor cores k=32 / 64 */
+    int32_t numeric_path;           /* numeric kernel that ran: 0 generic exact, 4 / 8 / 16 / 32 = specialised u64; 100 = fp32 SIMT, 132 / 164 = tensor cores k=32 / 64 */
     int32_t reserved;
 } bsp_stats;
 

@@ -420,6 +420,126 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
     cp_async_wait<0>();
 }
 
+// ---- fast path for large tiles (k = 16, 32) --------------------------------------------------
+// One thread per output-tile ROW (K accumulators in registers), 32/K tiles in flight per warp.
+// Per step the warp stages the B tile(s) in shared memory with cp.async (double buffered) and
+// every thread streams its own row of the A tile straight from global memory, two entries per
+// 128-bit load, two loads ahead of use.  Same arithmetic, detector and exact refold as above.
+template <int K>
+struct BigCfg {
+    static constexpr int GROUPS = 32 / K;                 // tiles in flight per warp (1 for k=32, 2 for k=16)
+    static constexpr int TILE_BYTES = K * K * 8;
+    static constexpr int CHUNKS = TILE_BYTES / 16;        // 16-byte chunks per tile
+    static constexpr int STAGE_BYTES = GROUPS * TILE_BYTES;
+};
+
+template <int K, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+numeric_bigtile_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restrict__ b_vals,
+                       const int64_t *__restrict__ pair_ptr, const int2 *__restrict__ pairs,
+                       const int2 *__restrict__ chunk_tiles, const int32_t *__restrict__ nchunks_ptr,
+                       uint64_t *__restrict__ c_vals, unsigned long long *__restrict__ refold_count)
+{
+    using Cfg = BigCfg<K>;
+    constexpr int STAGES = 2;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int grp = lane / K, r = lane % K;
+    const unsigned wbase = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)warp * (STAGES * Cfg::STAGE_BYTES);
+
+    const int nchunks = *nchunks_ptr;
+    const int g = (blockIdx.x * WARPS + warp) * Cfg::GROUPS + grp;
+    int t = 0, n = 0;
+    const int2 *prs = pairs;
+    if (g < nchunks) {
+        const int2 ct = chunk_tiles[g];
+        if (ct.x < ct.y) {
+            const int64_t p0 = pair_ptr[ct.x];
+            t = ct.x;
+            n = (int)(pair_ptr[ct.y] - p0);
+            prs = pairs + p0;
+        }
+    }
+    int steps = n;
+#pragma unroll
+    for (int d = 16; d; d >>= 1) steps = max(steps, __shfl_xor_sync(0xffffffffu, steps, d));
+    if (steps == 0) return;
+
+    // the warp copies the B tiles of its groups for one step: every cp.async moves 512 contiguous bytes
+    auto issue = [&](int ST, int bi, bool valid) {
+        const unsigned sbase = wbase + ST * Cfg::STAGE_BYTES;
+#pragma unroll
+        for (int q = 0; q < Cfg::GROUPS; q++) {
+            const int qb = __shfl_sync(0xffffffffu, bi, q * K);
+            const unsigned nbytes = __shfl_sync(0xffffffffu, (int)valid, q * K) ? 16u : 0u;
+            const unsigned char *src = reinterpret_cast<const unsigned char *>(b_vals) + (size_t)(unsigned)qb * Cfg::TILE_BYTES;
+#pragma unroll
+            for (int x = 0; x < Cfg::CHUNKS / 32; x++)
+                cp_async16_cg(sbase + q * Cfg::TILE_BYTES + (x * 32 + lane) * 16, src + (x * 32 + lane) * 16, nbytes);
+        }
+    };
+
+    const int n_last = max(n - 1, 0);
+    int2 cur = __ldcs(prs); // pair of the current step, nxt = pair of the next one
+    int2 nxt = __ldcs(prs + min(1, n_last));
+    issue(0, cur.y & 0x7fffffff, n > 0);
+    cp_async_commit();
+
+    uint64_t acc[K];
+    uint32_t flag = 0;
+#pragma unroll
+    for (int c = 0; c < K; c++) acc[c] = 0;
+
+    for (int k = 0; k < steps; k++) {
+        cp_async_wait<0>();
+        __syncwarp();
+        issue((k + 1) & 1, nxt.y & 0x7fffffff, k + 1 < n);
+        cp_async_commit();
+        const int2 nn = __ldcs(prs + min(k + 2, n_last));
+        if (k < n) {
+            const unsigned bsm = wbase + (k & 1) * Cfg::STAGE_BYTES + grp * Cfg::TILE_BYTES;
+            const ulonglong2 *arow = reinterpret_cast<const ulonglong2 *>(a_vals + (size_t)cur.x * (K * K) + (size_t)r * K);
+            ulonglong2 a0 = arow[0], a1 = arow[1]; // two loads in flight ahead of use
+#pragma unroll
+            for (int j2 = 0; j2 < K / 2; j2++) {
+                const ulonglong2 av = a0;
+                a0 = a1;
+                if (j2 + 2 < K / 2) a1 = arow[j2 + 2];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const uint64_t a = h ? av.y : av.x;
+                    const int j = 2 * j2 + h;
+#pragma unroll
+                    for (int c2 = 0; c2 < K / 2; c2++) {
+                        const ulonglong2 bv = lds128(bsm + (j * (K / 2) + c2) * 16); // broadcast inside the group
+                        mac_flag(acc[2 * c2], flag, a, bv.x);
+                        mac_flag(acc[2 * c2 + 1], flag, a, bv.y);
+                    }
+                }
+            }
+            if (cur.y < 0) { // last pair of the tile
+                if (flag == 0xffffffffu) {
+                    uint64_t exact[K];
+                    refold_row_exact<K>(a_vals, b_vals, pairs, pair_ptr[t], (prs - pairs) + k + 1, r, exact);
+#pragma unroll
+                    for (int c = 0; c < K; c++) acc[c] = exact[c];
+                    atomicAdd(refold_count, 1ull);
+                }
+                ulonglong2 *out = reinterpret_cast<ulonglong2 *>(c_vals + (size_t)t * (K * K) + (size_t)r * K);
+#pragma unroll
+                for (int i = 0; i < K / 2; i++) __stcs(&out[i], make_ulonglong2(acc[2 * i], acc[2 * i + 1]));
+#pragma unroll
+                for (int c = 0; c < K; c++) acc[c] = 0;
+                flag = 0;
+                t++;
+            }
+        }
+        cur = nxt;
+        nxt = nn;
+    }
+    cp_async_wait<0>();
+}
+
 struct NumericTuning { int Q; int panel_mb; int stages; int warps; bool q_forced; };
 
 NumericTuning numeric_tuning()
@@ -432,14 +552,14 @@ NumericTuning numeric_tuning()
     return tn;
 }
 
-template <int K, int STAGES, int WARPS>
-int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym, int nbr,
-                    const int32_t *c_rowptr, uint64_t *c_vals, const NumericTuning &tn)
+// chunk schedule shared by the fast kernels; returns the device arrays (caller releases them)
+struct ChunkSchedule { int32_t *seg_ts, *seg_nch, *seg_off; int2 *chunk_tiles; int max_chunks; int64_t nseg; };
+
+int build_schedule(bsp_ctx *ctx, const bsp_mat *B, const bsp_symbolic_out *sym, int nbr, const int32_t *c_rowptr,
+                   int tile_bytes, const NumericTuning &tn, ChunkSchedule *cs)
 {
-    using Cfg = RowsCfg<K>;
-    const int groups_per_cta = WARPS * Cfg::GROUPS;
     // panels: keep the touched part of B well inside L2
-    const int64_t b_bytes = B->nnzb * (int64_t)K * K * 8;
+    const int64_t b_bytes = B->nnzb * (int64_t)tile_bytes;
     int npanels = (int)((b_bytes + (int64_t)tn.panel_mb * (1 << 20) - 1) / ((int64_t)tn.panel_mb * (1 << 20)));
     if (npanels < 1) npanels = 1;
     if (npanels > 64) npanels = 64;
@@ -452,35 +572,70 @@ int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_
         const int64_t avg4 = 4 * (sym->nprod / sym->nnzb_c);
         if (avg4 > Q) Q = (int)(avg4 > 8192 ? 8192 : avg4);
     }
-    const int64_t nseg = (int64_t)nbr * npanels;
-    const int64_t max_chunks64 = sym->nprod / Q + nseg + 1;
+    if (!tn.q_forced && tile_bytes >= 2048) Q = Q / 4 > 8 ? Q / 4 : 8; // big tiles: a step is 8-64x the work
+    cs->nseg = (int64_t)nbr * npanels;
+    const int64_t max_chunks64 = sym->nprod / Q + cs->nseg + 1;
     if (max_chunks64 > 0x7fffff00LL) BSP_FAIL(ctx, BSP_ERR_LIMIT, "numeric pass: too many chunks");
-    const int max_chunks = (int)max_chunks64;
-
-    int32_t *seg_ts = nullptr, *seg_nch = nullptr, *seg_off = nullptr;
-    int2 *chunk_tiles = nullptr;
-    BSP_TRY(bsp_alloc(ctx, &seg_ts, (size_t)nseg + 1));
-    BSP_TRY(bsp_alloc(ctx, &seg_nch, (size_t)nseg + 1));
-    BSP_TRY(bsp_alloc(ctx, &seg_off, (size_t)nseg + 1));
-    BSP_TRY(bsp_alloc(ctx, &chunk_tiles, (size_t)max_chunks));
-    seg_bounds_kernel<<<(unsigned)((nseg + 1 + 255) / 256), 256, 0, ctx->stream>>>(nbr, npanels, panel_w, c_rowptr,
-                                                                                   sym->c_colidx, sym->pair_ptr, Q,
-                                                                                   seg_ts, seg_nch);
+    cs->max_chunks = (int)max_chunks64;
+    cs->seg_ts = cs->seg_nch = cs->seg_off = nullptr;
+    cs->chunk_tiles = nullptr;
+    BSP_TRY(bsp_alloc(ctx, &cs->seg_ts, (size_t)cs->nseg + 1));
+    BSP_TRY(bsp_alloc(ctx, &cs->seg_nch, (size_t)cs->nseg + 1));
+    BSP_TRY(bsp_alloc(ctx, &cs->seg_off, (size_t)cs->nseg + 1));
+    BSP_TRY(bsp_alloc(ctx, &cs->chunk_tiles, (size_t)cs->max_chunks));
+    seg_bounds_kernel<<<(unsigned)((cs->nseg + 1 + 255) / 256), 256, 0, ctx->stream>>>(
+        nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, cs->seg_ts, cs->seg_nch);
     BSP_LAUNCH_CHECK(ctx);
-    BSP_TRY(bsp_scan_i32(ctx, seg_nch, seg_off, nseg + 1, nullptr));
-    chunk_fill_kernel<<<(unsigned)((max_chunks + 255) / 256), 256, 0, ctx->stream>>>(
-        nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, seg_ts, seg_off, chunk_tiles);
+    BSP_TRY(bsp_scan_i32(ctx, cs->seg_nch, cs->seg_off, cs->nseg + 1, nullptr));
+    chunk_fill_kernel<<<(unsigned)((cs->max_chunks + 255) / 256), 256, 0, ctx->stream>>>(
+        nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, cs->seg_ts, cs->seg_off, cs->chunk_tiles);
     BSP_LAUNCH_CHECK(ctx);
-
     bsp_trace_mark(ctx, "num_schedule");
+    return BSP_OK;
+}
+
+void release_schedule(bsp_ctx *ctx, ChunkSchedule *cs)
+{
+    bsp_release(ctx, cs->seg_ts); bsp_release(ctx, cs->seg_nch); bsp_release(ctx, cs->seg_off); bsp_release(ctx, cs->chunk_tiles);
+}
+
+template <int K, int STAGES, int WARPS>
+int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym, int nbr,
+                    const int32_t *c_rowptr, uint64_t *c_vals, const NumericTuning &tn)
+{
+    using Cfg = RowsCfg<K>;
+    const int groups_per_cta = WARPS * Cfg::GROUPS;
+    ChunkSchedule cs;
+    BSP_TRY(build_schedule(ctx, B, sym, nbr, c_rowptr, Cfg::TILE_BYTES, tn, &cs));
     const size_t smem = (size_t)WARPS * STAGES * Cfg::STAGE_BYTES;
     auto kern = numeric_rows_kernel<K, STAGES, WARPS>;
     BSP_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int grid = (max_chunks + groups_per_cta - 1) / groups_per_cta;
-    kern<<<grid, WARPS * 32, smem, ctx->stream>>>(A->vals, B->vals, sym->pair_ptr, sym->pairs, chunk_tiles,
-                                                  seg_off + nseg, c_vals, (unsigned long long *)ctx->d_counters);
+    const int grid = (cs.max_chunks + groups_per_cta - 1) / groups_per_cta;
+    kern<<<grid, WARPS * 32, smem, ctx->stream>>>(A->vals, B->vals, sym->pair_ptr, sym->pairs, cs.chunk_tiles,
+                                                  cs.seg_off + cs.nseg, c_vals, (unsigned long long *)ctx->d_counters);
     BSP_LAUNCH_CHECK(ctx);
-    bsp_release(ctx, seg_ts); bsp_release(ctx, seg_nch); bsp_release(ctx, seg_off); bsp_release(ctx, chunk_tiles);
+    release_schedule(ctx, &cs);
+    return BSP_OK;
+}
+
+template <int K>
+int launch_bigtile(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym, int nbr,
+                   const int32_t *c_rowptr, uint64_t *c_vals)
+{
+    using Cfg = BigCfg<K>;
+    constexpr int WARPS = 4;
+    const NumericTuning tn = numeric_tuning();
+    ChunkSchedule cs;
+    BSP_TRY(build_schedule(ctx, B, sym, nbr, c_rowptr, Cfg::TILE_BYTES, tn, &cs));
+    const size_t smem = (size_t)WARPS * 2 * Cfg::STAGE_BYTES;
+    auto kern = numeric_bigtile_kernel<K, WARPS>;
+    BSP_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int groups_per_cta = WARPS * Cfg::GROUPS;
+    const int grid = (cs.max_chunks + groups_per_cta - 1) / groups_per_cta;
+    kern<<<grid, WARPS * 32, smem, ctx->stream>>>(A->vals, B->vals, sym->pair_ptr, sym->pairs, cs.chunk_tiles,
+                                                  cs.seg_off + cs.nseg, c_vals, (unsigned long long *)ctx->d_counters);
+    BSP_LAUNCH_CHECK(ctx);
+    release_schedule(ctx, &cs);
     return BSP_OK;
 }
 
@@ -504,10 +659,12 @@ int bsp_numeric(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
     if (path) *path = 0;
     if (sym->nnzb_c == 0) return BSP_OK;
     const int k = A->k;
-    if (!ctx->force_generic && (k == 4 || k == 8)) {
+    if (!ctx->force_generic && (k == 4 || k == 8 || k == 16 || k == 32)) {
         BSP_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(unsigned long long), ctx->stream));
         if (k == 8) BSP_TRY(launch_rows<8>(ctx, A, B, sym, A->nbr, sym->c_rowptr, c_vals));
-        else BSP_TRY(launch_rows<4>(ctx, A, B, sym, A->nbr, sym->c_rowptr, c_vals));
+        else if (k == 4) BSP_TRY(launch_rows<4>(ctx, A, B, sym, A->nbr, sym->c_rowptr, c_vals));
+        else if (k == 16) BSP_TRY(launch_bigtile<16>(ctx, A, B, sym, A->nbr, sym->c_rowptr, c_vals));
+        else BSP_TRY(launch_bigtile<32>(ctx, A, B, sym, A->nbr, sym->c_rowptr, c_vals));
         if (path) *path = k;
         if (exact_refolds) {
             unsigned long long *h = (unsigned long long *)((char *)ctx->pinned + 64);
