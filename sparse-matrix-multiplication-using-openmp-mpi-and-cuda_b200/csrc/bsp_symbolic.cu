@@ -245,16 +245,31 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     //    its A entry by binary search in the offset table, read its block column from B once,
     //    keep it in shared memory (in the area the pairs will occupy later) and set its bit
     int *tmpc = (int *)sp;
-#pragma unroll 4
-    for (int x = tid; x < P; x += FILL_THREADS) {
-        int lo = 0, hi = nA; // last entry with offset <= x
+    // every thread owns a contiguous run of products [x0, x1): one binary search for the A entry
+    // of x0, then it walks forward (runs are ~P/512 long, so consecutive lanes read consecutive
+    // memory and the run length being odd keeps the shared-memory stores conflict-free)
+    int per = (P + FILL_THREADS - 1) / FILL_THREADS;
+    per |= 1;
+    const int x0 = min(tid * per, P), x1 = min(x0 + per, P);
+    int e_run = 0;
+    if (x0 < x1) {
+        int lo = 0, hi = nA; // last entry with offset <= x0
         while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
-            if (aent[mid].y <= x) lo = mid; else hi = mid;
+            if (aent[mid].y <= x0) lo = mid; else hi = mid;
         }
-        const int c = b_colidx[aent[lo].x + (x - aent[lo].y)];
-        tmpc[x] = c;
-        atomicOr(&bm[c >> 5], 1u << (c & 31));
+        e_run = lo;
+    }
+    {
+        int e = e_run;
+        int2 ae = aent[e];
+        int next_off = aent[e + 1].y;
+        for (int x = x0; x < x1; x++) {
+            while (x >= next_off) { e++; ae = aent[e]; next_off = aent[e + 1].y; }
+            const int c = b_colidx[ae.x + (x - ae.y)];
+            tmpc[x] = c;
+            atomicOr(&bm[c >> 5], 1u << (c & 31));
+        }
     }
     __syncthreads();
     // 2. rank table + sorted colidx of the C row
@@ -278,7 +293,7 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     }
     __syncthreads();
     // 3. output tile of every product (16-bit rank in the row) + pairs per tile
-    for (int x = tid; x < P; x += FILL_THREADS) {
+    for (int x = x0; x < x1; x++) {
         const int c = tmpc[x];
         const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
         prodt[x] = (unsigned short)t;
@@ -305,15 +320,15 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         // 5a. every tile has few pairs: place all products at once (cursor bumped atomically, any
         //     order), then put each tile's pairs in ascending A index -- which is ascending j,
         //     because the A row is sorted -- with a tiny insertion sort, one thread per tile.
-#pragma unroll 2
-        for (int x = tid; x < P; x += FILL_THREADS) {
-            int lo = 0, hi = nA;
-            while (hi - lo > 1) {
-                const int mid = (lo + hi) >> 1;
-                if (aent[mid].y <= x) lo = mid; else hi = mid;
+        {
+            int e = e_run;
+            int2 ae = aent[e];
+            int next_off = aent[e + 1].y;
+            for (int x = x0; x < x1; x++) {
+                while (x >= next_off) { e++; ae = aent[e]; next_off = aent[e + 1].y; }
+                const int pos = atomicAdd(&cur[prodt[x]], 1);
+                sp[pos] = make_int2(a0 + e, ae.x + (x - ae.y));
             }
-            const int pos = atomicAdd(&cur[prodt[x]], 1);
-            sp[pos] = make_int2(a0 + lo, aent[lo].x + (x - aent[lo].y));
         }
         __syncthreads();
         for (int t = tid; t < T; t += FILL_THREADS) {
