@@ -230,6 +230,7 @@ def run_chain(torch, dist, ctx, rank, world, steps, warmup):
     mats = [ctx.matrix_from_coo(*chain_matrix(i)) for i in range(mine[0], mine[1] + 1)] if mine else []
     nprod = 0
     sent = 0
+    gb = bsp_dist.GroupBroadcaster(dist, torch, len(parts), "cuda") if world > 1 else None
 
     def sync():
         torch.cuda.synchronize()
@@ -261,15 +262,28 @@ def run_chain(torch, dist, ctx, rank, world, steps, warmup):
         def recv(src):
             return bsp_dist.payload_to_matrix(torch, ctx, bsp_dist.recv_payload(dist, torch, src, "cuda"))
 
-        def mul_panel(a, b, lo, hi):
+        def mul_panel(a, b, rng):
             nonlocal nprod
             s2 = bspgemm.Stats()
-            c = ctx.helper(a, b, stats=s2, panel=(lo, hi))
+            c = ctx.helper(a, b, stats=s2, panel=rng)
             nprod += s2.nprod
             return c
+
+        def send_rows(m, lo, hi, dst):
+            nonlocal sent
+            pl = bsp_dist.slice_rows_payload(torch, bsp_dist.matrix_to_payload(torch, m), lo, hi)
+            sent += pl.nbytes
+            bsp_dist.send_payload(dist, pl, dst)
+
+        def bcast(m, src, grp):
+            nonlocal sent
+            pl = bsp_dist.matrix_to_payload(torch, m) if m is not None else None
+            if pl is not None:
+                sent += pl.nbytes
+            return bsp_dist.payload_to_matrix(torch, ctx, gb.bcast(pl, src, grp))
         if os.environ.get("BSP_CHAIN_MERGE", "panels") == "rank0":  # the reference's shape: receiver multiplies alone
             return bsp_dist.tree_merge(rank, len(parts), partial, mul, send, recv)
-        return bsp_dist.tree_merge_panels(rank, len(parts), partial, send, recv,
+        return bsp_dist.tree_merge_panels(rank, len(parts), partial, send, recv, send_rows, bcast,
                                           lambda m: bsp_dist.device_row_weights(torch, m), mul_panel, ctx.concat_panels)
 
     res = None

@@ -172,57 +172,62 @@ def tree_merge(rank, nparts, partial, multiply, send, recv):
     return held if rank == 0 else None
 
 
-def tree_merge_panels(rank, nparts, partial, send, recv, row_weights, multiply_panel, concat):
+def merge_groups(nparts):
+    """All rank groups that tree_merge_panels uses, in schedule order: [(step, [ranks...]), ...]."""
+    out = []
+    s = 1
+    while s < nparts:
+        for g in range(0, nparts, 2 * s):
+            if g + s < nparts:
+                out.append((s, list(range(g, min(g + 2 * s, nparts)))))
+        s *= 2
+    return out
+
+
+def tree_merge_panels(rank, nparts, partial, send, recv, send_rows, bcast, row_weights, multiply, concat):
     """Step-doubling merge in which every product is ROW-PANEL SHARDED over the ranks of its
     subtree instead of being computed by the receiving rank alone (the reference's rank 0
     multiplies the P partials sequentially, cu:569-571, which leaves P-1 ranks idle exactly
     where the chain is most expensive).  The association tree is unchanged and every output
     element is still folded by one thread in reference order, so the result is bit-identical.
 
-    For the merge of (g, g+s): ranks g..g+2s-1 all receive left (held by g) and right (held by
-    g+s), each multiplies one block-row panel of left by right (panels balanced by
-    row_weights(left)), the panels are gathered on g and concatenated.
-      send(obj, dst) / recv(src) -> obj        move a matrix
-      row_weights(left) -> 1-D array           estimated work per block row
-      multiply_panel(left, right, lo, hi)      block rows [lo, hi) of left*right
-      concat(list_of_panels)                   one matrix
+    For the merge of (g, g+s) the group is ranks g..g+2s-1: rank g scatters block-row panels of
+    left (balanced by row_weights(left)), rank g+s broadcasts right, every rank multiplies its
+    panel by right, the panel products are gathered on g and concatenated.
+      send(obj, dst) / recv(src) -> obj            move a whole matrix
+      send_rows(obj, lo, hi, dst)                  move block rows [lo, hi) of a matrix (same row space)
+      bcast(obj_or_None, src, group) -> obj        broadcast a matrix inside `group` (list of ranks)
+      row_weights(left) -> 1-D array               estimated work per block row
+      multiply(left_rows, right)                   product (left_rows holds only this rank's panel)
+      concat(list_of_panels)                       one matrix
     Returns the final product on rank 0, None elsewhere."""
     held = partial
-    s = 1
-    while s < nparts:
-        for g in range(0, nparts, 2 * s):
-            if g + s >= nparts:
-                continue
-            group = list(range(g, min(g + 2 * s, nparts)))
-            if rank not in group:
-                continue
-            # 1. left from g, right from g+s, to everybody in the group
-            if rank == g:
-                left = held
-                for r in group:
-                    if r != g:
-                        send(left, r)
-            else:
-                left = recv(g)
-            if rank == g + s:
-                right = held
-                for r in group:
-                    if r != g + s:
-                        send(right, r)
-            else:
-                right = recv(g + s)
-            # 2. this rank's panel
-            bounds = balanced_panels(row_weights(left), len(group))
-            me = group.index(rank)
-            panel = multiply_panel(left, right, bounds[me], bounds[me + 1])
-            # 3. gather on g
-            if rank == g:
-                panels = [panel] + [recv(r) for r in group[1:]]
-                held = concat(panels)
-            else:
-                send(panel, g)
-                held = None
-        s *= 2
+    for s, group in merge_groups(nparts):
+        if rank not in group:
+            continue
+        g = group[0]
+        # 1. left: block-row panels from g;  right: from g+s to everybody in the group
+        if rank == g:
+            bounds = balanced_panels(row_weights(held), len(group))
+            for i, r in enumerate(group):
+                if r != g:
+                    send_rows(held, bounds[i], bounds[i + 1], r)
+            left_rows = (held, bounds[0], bounds[1])
+        else:
+            left_rows = (recv(g), None, None)
+        right = bcast(held if rank == g + s else None, g + s, group)
+        # 2. this rank's panel
+        if rank == g:
+            panel = multiply(left_rows[0], right, (left_rows[1], left_rows[2]))
+        else:
+            panel = multiply(left_rows[0], right, None)
+        # 3. gather on g
+        if rank == g:
+            panels = [panel] + [recv(r) for r in group[1:]]
+            held = concat(panels)
+        else:
+            send(panel, g)
+            held = None
     return held if rank == 0 else None
 
 
@@ -233,3 +238,45 @@ def device_row_weights(torch, mat):
     torch.cuda.synchronize()
     mat.export_device(rp.data_ptr(), 0, 0)
     return np.diff(rp.cpu().numpy())
+
+
+def slice_rows_payload(torch, pl, lo, hi):
+    """Payload holding only block rows [lo, hi) of `pl` (same row space; CSR slices are contiguous)."""
+    nbr = pl.rowptr.numel() - 1
+    lo, hi = max(0, min(lo, nbr)), max(0, min(hi, nbr))
+    s0, s1 = int(pl.rowptr[lo].item()), int(pl.rowptr[hi].item())
+    rows, cols, k = [int(x) for x in pl.header[:3].tolist()]
+    kk = k * k
+    rowptr = (torch.clamp(pl.rowptr, s0, s1) - s0).to(torch.int32)
+    header = pl.header.clone()
+    header[5] = s1 - s0
+    return Payload(header, rowptr, pl.colidx[s0:s1].contiguous(), pl.vals[s0 * kk:s1 * kk].contiguous())
+
+
+class GroupBroadcaster:
+    """Broadcast of a Payload inside the rank groups of tree_merge_panels, over pre-created
+    torch.distributed sub-groups (NCCL: one tree/ring broadcast instead of len(group)-1 sends)."""
+
+    def __init__(self, dist, torch, nparts, device):
+        self.dist, self.torch, self.device = dist, torch, device
+        self.groups = {}
+        for _, ranks in merge_groups(nparts):
+            key = tuple(ranks)
+            if key not in self.groups:  # new_group is collective over the whole world: same order everywhere
+                self.groups[key] = dist.new_group(ranks=ranks)
+
+    def bcast(self, pl, src, ranks):
+        dist, torch = self.dist, self.torch
+        grp = self.groups[tuple(ranks)]
+        header = pl.header if pl is not None else torch.empty(HEADER_LEN, dtype=torch.int64, device=self.device)
+        dist.broadcast(header, src, group=grp)
+        rows, cols, k, nbr, nbc, nnzb = [int(x) for x in header.cpu().tolist()]
+        if pl is None:
+            pl = Payload(header, torch.empty(nbr + 1, dtype=torch.int32, device=self.device),
+                         torch.empty(nnzb, dtype=torch.int32, device=self.device),
+                         torch.empty(nnzb * k * k, dtype=torch.int64, device=self.device))
+        dist.broadcast(pl.rowptr, src, group=grp)
+        if nnzb:
+            dist.broadcast(pl.colidx, src, group=grp)
+            dist.broadcast(pl.vals, src, group=grp)
+        return pl

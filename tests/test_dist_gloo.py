@@ -26,8 +26,8 @@ def _free_port():
 
 def _omat_to_payload(m):
     br, bc, v = m.coo()
-    nbr = int(br.max()) + 1 if br.size else 0
-    nbc = int(bc.max()) + 1 if bc.size else 0
+    nbr = m.rows // m.k  # the generators use coordinates < rows/k; keeps the row space of slices identical
+    nbc = m.cols // m.k
     rowptr = np.zeros(nbr + 1, np.int32)
     np.add.at(rowptr, br + 1, 1)
     rowptr = np.cumsum(rowptr).astype(np.int32)
@@ -56,8 +56,7 @@ def _concat(panels):
 
 
 def _weights(m):
-    br = m.coo()[0]
-    return np.bincount(br, minlength=(int(br.max()) + 1 if br.size else 1))
+    return np.bincount(m.coo()[0], minlength=m.rows // m.k)
 
 
 def _worker(rank, world, port, n_mats, k, G, outdir, panels=False):
@@ -73,9 +72,15 @@ def _worker(rank, world, port, n_mats, k, G, outdir, panels=False):
         send = lambda m, dst: bsp_dist.send_payload(dist, _omat_to_payload(m), dst)  # noqa: E731
         recv = lambda src: _payload_to_omat(bsp_dist.recv_payload(dist, torch, src, "cpu"))  # noqa: E731
         if panels:
+            gb = bsp_dist.GroupBroadcaster(dist, torch, len(parts), "cpu")
             res = bsp_dist.tree_merge_panels(
-                rank, len(parts), partial, send, recv, _weights,
-                multiply_panel=lambda a, b, lo, hi: orc.multiply(_row_slice(a, lo, hi), b)[0], concat=_concat)
+                rank, len(parts), partial, send, recv,
+                send_rows=lambda m, lo, hi, dst: bsp_dist.send_payload(
+                    dist, bsp_dist.slice_rows_payload(torch, _omat_to_payload(m), lo, hi), dst),
+                bcast=lambda m, src, grp: _payload_to_omat(gb.bcast(_omat_to_payload(m) if m is not None else None, src, grp)),
+                row_weights=_weights,
+                multiply=lambda a, b, rng: orc.multiply(a if rng is None else _row_slice(a, rng[0], rng[1]), b)[0],
+                concat=_concat)
         else:
             res = bsp_dist.tree_merge(rank, len(parts), partial, multiply=lambda a, b: orc.multiply(a, b)[0],
                                       send=send, recv=recv)

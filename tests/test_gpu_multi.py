@@ -53,8 +53,13 @@ partial = ctx.helper2(mats)
 send = lambda m, dst: bsp_dist.send_payload(dist, bsp_dist.matrix_to_payload(torch, m), dst)
 recv = lambda src: bsp_dist.payload_to_matrix(torch, ctx, bsp_dist.recv_payload(dist, torch, src, "cuda"))
 if sys.argv[4] == "panels":
-    res = bsp_dist.tree_merge_panels(rank, len(parts), partial, send, recv, lambda m: bsp_dist.device_row_weights(torch, m),
-                                     lambda a, b, lo, hi: ctx.helper(a, b, panel=(lo, hi)), ctx.concat_panels)
+    gb = bsp_dist.GroupBroadcaster(dist, torch, len(parts), "cuda")
+    res = bsp_dist.tree_merge_panels(
+        rank, len(parts), partial, send, recv,
+        lambda m, lo, hi, dst: bsp_dist.send_payload(dist, bsp_dist.slice_rows_payload(torch, bsp_dist.matrix_to_payload(torch, m), lo, hi), dst),
+        lambda m, src, grp: bsp_dist.payload_to_matrix(torch, ctx, gb.bcast(bsp_dist.matrix_to_payload(torch, m) if m is not None else None, src, grp)),
+        lambda m: bsp_dist.device_row_weights(torch, m),
+        lambda a, b, rng: ctx.helper(a, b, panel=rng), ctx.concat_panels)
 else:
     res = bsp_dist.tree_merge(rank, len(parts), partial, lambda a, b: ctx.helper(a, b), send, recv)
 if rank == 0:
