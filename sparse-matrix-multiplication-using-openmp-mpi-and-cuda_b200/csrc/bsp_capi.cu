@@ -47,23 +47,27 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
 
     bsp_mat *c = nullptr;
     BSP_TRY(new_empty_like(ctx, A->rows, B->cols, A->k, A->nbr, B->nbc, &c, A->esize)); // cu:280-282
-    *C = c;
     BSP_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
     bsp_trace_mark(ctx, "start");
     bsp_symbolic_out sym;
-    BSP_TRY(bsp_symbolic(ctx, A, B, row_lo, row_hi, &sym));
-    BSP_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-    c->rowptr = sym.c_rowptr;
+    int rc = bsp_symbolic(ctx, A, B, row_lo, row_hi, &sym);
+    if (rc != BSP_OK) { delete c; return rc; }
+    c->rowptr = sym.c_rowptr; // from here on bsp_mat_free(c) releases the pattern arrays
     c->colidx = sym.c_colidx;
     c->nnzb = sym.nnzb_c;
-    BSP_TRY(bsp_alloc(ctx, (char **)&c->vals, (size_t)sym.nnzb_c * A->k * A->k * A->esize));
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+    rc = bsp_alloc(ctx, (char **)&c->vals, (size_t)sym.nnzb_c * A->k * A->k * A->esize);
     bsp_trace_mark(ctx, "alloc_c");
-    if (A->esize == 8) BSP_TRY(bsp_numeric(ctx, A, B, &sym, c->vals, &st.exact_refolds, &st.numeric_path));
-    else BSP_TRY(bsp_numeric_f32(ctx, A, B, &sym, (float *)c->vals, &st.numeric_path));
+    if (rc == BSP_OK) {
+        if (A->esize == 8) rc = bsp_numeric(ctx, A, B, &sym, c->vals, &st.exact_refolds, &st.numeric_path);
+        else rc = bsp_numeric_f32(ctx, A, B, &sym, (float *)c->vals, &st.numeric_path);
+    }
     bsp_trace_mark(ctx, "numeric");
-    BSP_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+    cudaEventRecord(ctx->ev[2], ctx->stream);
     bsp_release(ctx, sym.pair_ptr);
     bsp_release(ctx, sym.pairs);
+    if (rc != BSP_OK) { bsp_mat_free(ctx, c); return rc; }
+    *C = c;
     BSP_CUDA(ctx, cudaEventSynchronize(ctx->ev[2]));
     float ms01 = 0, ms12 = 0;
     BSP_CUDA(ctx, cudaEventElapsedTime(&ms01, ctx->ev[0], ctx->ev[1]));

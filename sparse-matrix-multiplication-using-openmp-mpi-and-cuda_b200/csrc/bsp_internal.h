@@ -110,6 +110,30 @@ static inline void bsp_trace_dump(bsp_ctx *ctx)
     ctx->ntrace = 0;
 }
 
+// Scratch allocations of one call: everything still registered is released when the guard
+// goes out of scope, so early returns on errors do not strand pool memory.  keep(p) hands a
+// buffer over to the caller (result arrays).
+struct bsp_scratch {
+    bsp_ctx *ctx;
+    void *ptrs[32];
+    int n;
+    explicit bsp_scratch(bsp_ctx *c) : ctx(c), n(0) {}
+    ~bsp_scratch() { for (int i = 0; i < n; i++) bsp_release(ctx, ptrs[i]); }
+    template <typename T> int alloc(T **p, size_t count)
+    {
+        const int rc = bsp_alloc(ctx, p, count);
+        if (rc == BSP_OK && n < 32) ptrs[n++] = *p;
+        return rc;
+    }
+    void keep(void *p)
+    {
+        for (int i = 0; i < n; i++)
+            if (ptrs[i] == p) { ptrs[i] = ptrs[--n]; return; }
+    }
+    bsp_scratch(const bsp_scratch &) = delete;
+    bsp_scratch &operator=(const bsp_scratch &) = delete;
+};
+
 #define BSP_LAUNCH_CHECK(ctx)                  \
     do {                                       \
         (ctx)->launches++;                     \

@@ -205,8 +205,9 @@ struct RowsCfg {
     static constexpr int CHUNKS = TILE_BYTES / 16;             // 16-byte chunks per tile (32 for k=8, 8 for k=4)
     static constexpr int TPI = CHUNKS >= 32 ? 1 : 32 / CHUNKS; // tiles moved by one warp-wide cp.async
     static constexpr int IPT = CHUNKS >= 32 ? CHUNKS / 32 : 1; // warp-wide cp.async instructions per tile
-    static constexpr int GROUP_STRIDE = 2 * TILE_BYTES + 32;   // A tile, B tile; +32 B shifts the next group by 8 banks
-    static constexpr int STAGE_BYTES = GROUPS * GROUP_STRIDE;  // per warp
+    static constexpr int GROUP_STRIDE = TILE_BYTES + 32;       // one tile per group; +32 B shifts the next group by 8 banks
+    static constexpr int STAGE_BYTES = GROUPS * GROUP_STRIDE;  // per warp: one set of tiles (A: single buffer, B: STAGES buffers)
+    __host__ __device__ static constexpr int WARP_BYTES(int stages) { return (1 + stages) * STAGE_BYTES; } // A + B stages
 };
 
 // position of 16-byte chunk i of row r inside the A tile: XOR swizzle so that the TPT threads
@@ -249,7 +250,7 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane / TPT, h = lane % TPT;
     // 32-bit shared-memory addresses, computed once
-    const unsigned wbase = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)warp * (STAGES * Cfg::STAGE_BYTES);
+    const unsigned wbase = (unsigned)__cvta_generic_to_shared(smem) + (unsigned)warp * Cfg::WARP_BYTES(STAGES);
 
     const int nchunks = *nchunks_ptr;
     const int g = (blockIdx.x * WARPS + warp) * Cfg::GROUPS + grp;
@@ -280,7 +281,7 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
     for (int part = 0; part < Cfg::IPT; part++) {
         const int nn = cn + 32 * part;
         dstA[part] = cq * Cfg::GROUP_STRIDE + a_chunk_offset<K>(nn / (K / 2), nn % (K / 2));
-        dstB[part] = cq * Cfg::GROUP_STRIDE + Cfg::TILE_BYTES + nn * 16;
+        dstB[part] = cq * Cfg::GROUP_STRIDE + nn * 16;
     }
 
     // The whole warp copies the tiles of all its groups for one step into stage ST: every
@@ -289,7 +290,7 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
     // steps: its copies become zero-size (nothing is read; thousands of idle groups re-reading
     // one dummy tile would serialise on a single L2 line).
     auto issue = [&](int ST, int ai, int bi) {
-        const unsigned sbase = wbase + ST * Cfg::STAGE_BYTES;
+        const unsigned abase = wbase, bbase = wbase + (1 + ST) * Cfg::STAGE_BYTES; // A: single buffer, B: stage ST
 #pragma unroll
         for (int q0 = 0; q0 < Cfg::GROUPS; q0 += Cfg::TPI) {
             const int src_lane = (q0 + cq) * TPT;
@@ -299,8 +300,8 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
             const size_t ia = (size_t)(unsigned)(qa & 0x7fffffff), ib = (size_t)(unsigned)qb;
 #pragma unroll
             for (int part = 0; part < Cfg::IPT; part++) {
-                cp_async16_ca(sbase + q0 * Cfg::GROUP_STRIDE + dstA[part], a_lane + ia * Cfg::TILE_BYTES + part * 512, nbytes);
-                cp_async16_cg(sbase + q0 * Cfg::GROUP_STRIDE + dstB[part], b_lane + ib * Cfg::TILE_BYTES + part * 512, nbytes);
+                cp_async16_ca(abase + q0 * Cfg::GROUP_STRIDE + dstA[part], a_lane + ia * Cfg::TILE_BYTES + part * 512, nbytes);
+                cp_async16_cg(bbase + q0 * Cfg::GROUP_STRIDE + dstB[part], b_lane + ib * Cfg::TILE_BYTES + part * 512, nbytes);
             }
         }
     };
@@ -335,17 +336,12 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
 
     auto step = [&](int ST, int k) {
         cp_async_wait<STAGES - 2>(); // this thread's copies for step k have landed
-        __syncwarp();                // ... and everybody else's; everybody is done reading step k-1's stage
+        __syncwarp();                // ... and everybody else's; everybody is done reading step k-1's B stage
+        // A rows of this step go to registers right away: the A tiles have a single buffer
+        // (12.5 instead of 16.5 KB of shared memory per warp -> one more CTA per SM)
+        uint64_t a_cur[RPT][K];
         {
-            const int kk = k + (STAGES - 1);
-            issue((ST + STAGES - 1) % STAGES, kk < n ? nx : (nx | (int)0x80000000), ny & 0x7fffffff);
-            lastq |= (kk < n && ny < 0 ? 1u : 0u) << (STAGES - 1);
-            { const int2 pr = __ldcs(prs + min(kk + 1, n_last)); nx = pr.x; ny = pr.y; }
-            cp_async_commit();
-        }
-        if (k < n) {
-            const unsigned st = gbase + ST * Cfg::STAGE_BYTES;
-            uint64_t a_cur[RPT][K];
+            const unsigned st = gbase;
 #pragma unroll
             for (int rr = 0; rr < RPT; rr++) {
                 const int r = h + TPT * rr;
@@ -360,7 +356,17 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
                     a_cur[rr][2 * i + 1] = v.y;
                 }
             }
-            const unsigned bsm = st + Cfg::TILE_BYTES;
+        }
+        __syncwarp(); // everybody holds its A rows: the A buffer may be overwritten
+        {
+            const int kk = k + (STAGES - 1);
+            issue((ST + STAGES - 1) % STAGES, kk < n ? nx : (nx | (int)0x80000000), ny & 0x7fffffff);
+            lastq |= (kk < n && ny < 0 ? 1u : 0u) << (STAGES - 1);
+            { const int2 pr = __ldcs(prs + min(kk + 1, n_last)); nx = pr.x; ny = pr.y; }
+            cp_async_commit();
+        }
+        if (k < n) {
+            const unsigned bsm = gbase + (1 + ST) * Cfg::STAGE_BYTES;
             // B row j+1 is fetched from shared memory while row j is being multiplied
             ulonglong2 bnext[K / 2];
 #pragma unroll
@@ -579,10 +585,11 @@ int build_schedule(bsp_ctx *ctx, const bsp_mat *B, const bsp_symbolic_out *sym, 
     cs->max_chunks = (int)max_chunks64;
     cs->seg_ts = cs->seg_nch = cs->seg_off = nullptr;
     cs->chunk_tiles = nullptr;
-    BSP_TRY(bsp_alloc(ctx, &cs->seg_ts, (size_t)cs->nseg + 1));
-    BSP_TRY(bsp_alloc(ctx, &cs->seg_nch, (size_t)cs->nseg + 1));
-    BSP_TRY(bsp_alloc(ctx, &cs->seg_off, (size_t)cs->nseg + 1));
-    BSP_TRY(bsp_alloc(ctx, &cs->chunk_tiles, (size_t)cs->max_chunks));
+    bsp_scratch sc(ctx);
+    BSP_TRY(sc.alloc(&cs->seg_ts, (size_t)cs->nseg + 1));
+    BSP_TRY(sc.alloc(&cs->seg_nch, (size_t)cs->nseg + 1));
+    BSP_TRY(sc.alloc(&cs->seg_off, (size_t)cs->nseg + 1));
+    BSP_TRY(sc.alloc(&cs->chunk_tiles, (size_t)cs->max_chunks));
     seg_bounds_kernel<<<(unsigned)((cs->nseg + 1 + 255) / 256), 256, 0, ctx->stream>>>(
         nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, cs->seg_ts, cs->seg_nch);
     BSP_LAUNCH_CHECK(ctx);
@@ -591,6 +598,7 @@ int build_schedule(bsp_ctx *ctx, const bsp_mat *B, const bsp_symbolic_out *sym, 
         nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, cs->seg_ts, cs->seg_off, cs->chunk_tiles);
     BSP_LAUNCH_CHECK(ctx);
     bsp_trace_mark(ctx, "num_schedule");
+    sc.keep(cs->seg_ts); sc.keep(cs->seg_nch); sc.keep(cs->seg_off); sc.keep(cs->chunk_tiles); // released by release_schedule
     return BSP_OK;
 }
 
@@ -607,7 +615,7 @@ int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_
     const int groups_per_cta = WARPS * Cfg::GROUPS;
     ChunkSchedule cs;
     BSP_TRY(build_schedule(ctx, B, sym, nbr, c_rowptr, Cfg::TILE_BYTES, tn, &cs));
-    const size_t smem = (size_t)WARPS * STAGES * Cfg::STAGE_BYTES;
+    const size_t smem = (size_t)WARPS * Cfg::WARP_BYTES(STAGES);
     auto kern = numeric_rows_kernel<K, STAGES, WARPS>;
     BSP_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = (cs.max_chunks + groups_per_cta - 1) / groups_per_cta;

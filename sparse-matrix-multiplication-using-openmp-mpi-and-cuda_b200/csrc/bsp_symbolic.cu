@@ -565,13 +565,14 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
 
     int32_t *row_cnt = nullptr, *row_prod = nullptr, *lists = nullptr, *counts = nullptr, *heavy = nullptr;
     int64_t *row_prod_ptr = nullptr;
-    BSP_TRY(bsp_alloc(ctx, &row_cnt, (size_t)nbr + 1));
-    BSP_TRY(bsp_alloc(ctx, &row_prod, (size_t)nbr + 1));
-    BSP_TRY(bsp_alloc(ctx, &row_prod_ptr, (size_t)nbr + 1));
-    BSP_TRY(bsp_alloc(ctx, &lists, (size_t)NCLASS * (nbr > 0 ? nbr : 1)));
-    BSP_TRY(bsp_alloc(ctx, &counts, (size_t)NCLASS + 1)); // [NCLASS] = number of heavy rows of the count pass
-    BSP_TRY(bsp_alloc(ctx, &heavy, (size_t)(nbr > 0 ? nbr : 1)));
-    BSP_TRY(bsp_alloc(ctx, &out->c_rowptr, (size_t)nbr + 1));
+    bsp_scratch sc(ctx); // releases everything below on any return; the outputs are handed over at the end
+    BSP_TRY(sc.alloc(&row_cnt, (size_t)nbr + 1));
+    BSP_TRY(sc.alloc(&row_prod, (size_t)nbr + 1));
+    BSP_TRY(sc.alloc(&row_prod_ptr, (size_t)nbr + 1));
+    BSP_TRY(sc.alloc(&lists, (size_t)NCLASS * (nbr > 0 ? nbr : 1)));
+    BSP_TRY(sc.alloc(&counts, (size_t)NCLASS + 1)); // [NCLASS] = number of heavy rows of the count pass
+    BSP_TRY(sc.alloc(&heavy, (size_t)(nbr > 0 ? nbr : 1)));
+    BSP_TRY(sc.alloc(&out->c_rowptr, (size_t)nbr + 1));
     BSP_CUDA(ctx, cudaMemsetAsync(row_cnt + nbr, 0, sizeof(int32_t), ctx->stream));
     BSP_CUDA(ctx, cudaMemsetAsync(row_prod + nbr, 0, sizeof(int32_t), ctx->stream));
     BSP_CUDA(ctx, cudaMemsetAsync(counts, 0, (NCLASS + 1) * sizeof(int32_t), ctx->stream));
@@ -639,9 +640,9 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     for (int c = 0; c < NCLASS; c++) ncls[c] = h_counts[c];
     if (out->nnzb_c < 0) BSP_FAIL(ctx, BSP_ERR_LIMIT, "product has more than 2^31-1 tiles");
 
-    BSP_TRY(bsp_alloc(ctx, &out->c_colidx, (size_t)out->nnzb_c));
-    BSP_TRY(bsp_alloc(ctx, &out->pair_ptr, (size_t)out->nnzb_c + 1));
-    BSP_TRY(bsp_alloc(ctx, &out->pairs, (size_t)out->nprod));
+    BSP_TRY(sc.alloc(&out->c_colidx, (size_t)out->nnzb_c));
+    BSP_TRY(sc.alloc(&out->pair_ptr, (size_t)out->nnzb_c + 1));
+    BSP_TRY(sc.alloc(&out->pairs, (size_t)out->nprod));
     // every row writes its own slots; the closing entry pair_ptr[nnzb_c] = nprod comes from the row scan
     BSP_CUDA(ctx, cudaMemcpyAsync(out->pair_ptr + out->nnzb_c, row_prod_ptr + nbr, sizeof(int64_t),
                                   cudaMemcpyDeviceToDevice, ctx->stream));
@@ -664,11 +665,6 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         BSP_LAUNCH_CHECK(ctx);
     }
     bsp_trace_mark(ctx, "sym_fill");
-    bsp_release(ctx, row_cnt);
-    bsp_release(ctx, row_prod);
-    bsp_release(ctx, row_prod_ptr);
-    bsp_release(ctx, lists);
-    bsp_release(ctx, counts);
-    bsp_release(ctx, heavy);
+    sc.keep(out->c_rowptr); sc.keep(out->c_colidx); sc.keep(out->pair_ptr); sc.keep(out->pairs); // now the caller's
     return BSP_OK;
 }
