@@ -100,6 +100,72 @@ int clone_mat(bsp_ctx *ctx, const bsp_mat *s, bsp_mat **out)
     return BSP_OK;
 }
 
+// One tree level of a chain as ONE product (see bsp_matrix.cu, "batching of independent
+// products"): worthwhile when the level has several small products, whose cost is launch and
+// synchronisation latency (about 0.2 ms each), not work.
+int batched_level(bsp_ctx *ctx, const std::vector<bsp_mat *> &as, const std::vector<bsp_mat *> &bs,
+                  std::vector<bsp_mat *> *cs, bsp_stats *st)
+{
+    const int m = (int)as.size();
+    const int k = as[0]->k, esize = as[0]->esize;
+    int64_t na = 0, nb = 0;
+    int32_t ra = 0, rb = 0, nbc_a = 0, nbc_b = 0;
+    std::vector<int32_t> shifts(m), limits(m);
+    for (int i = 0; i < m; i++) {
+        shifts[i] = rb; limits[i] = bs[i]->nbr;
+        na += as[i]->nnzb; nb += bs[i]->nnzb; ra += as[i]->nbr; rb += bs[i]->nbr;
+        nbc_b = bs[i]->nbc > nbc_b ? bs[i]->nbc : nbc_b;
+    }
+    nbc_a = rb;
+    bsp_mat *A = nullptr, *B = nullptr, *C = nullptr;
+    int rc = new_empty_like(ctx, as[0]->rows, as[0]->cols, k, ra, nbc_a, &A, esize);
+    if (rc == BSP_OK) rc = new_empty_like(ctx, bs[0]->rows, bs[0]->cols, k, rb, nbc_b, &B, esize);
+    auto fill = [&](bsp_mat *M, int64_t nnzb) {
+        M->nnzb = nnzb;
+        int r = bsp_alloc(ctx, &M->rowptr, (size_t)M->nbr + 1);
+        if (r == BSP_OK) r = bsp_alloc(ctx, &M->colidx, (size_t)nnzb);
+        if (r == BSP_OK) r = bsp_alloc(ctx, (char **)&M->vals, (size_t)nnzb * k * k * esize);
+        return r;
+    };
+    if (rc == BSP_OK) rc = fill(A, na);
+    if (rc == BSP_OK) rc = fill(B, nb);
+    if (rc == BSP_OK) rc = bsp_stack_rows_device(ctx, as.data(), m, shifts.data(), limits.data(), 0x7ffffff0, A);
+    if (rc == BSP_OK) rc = bsp_stack_rows_device(ctx, bs.data(), m, nullptr, nullptr, 0, B);
+    if (rc == BSP_OK) rc = spgemm_impl(ctx, A, B, 0, INT32_MAX, &C, st);
+    bsp_mat_free(ctx, A);
+    bsp_mat_free(ctx, B);
+    if (rc != BSP_OK) { bsp_mat_free(ctx, C); return rc; }
+    // row pointers of the stacked product at the block boundaries -> tile ranges of the parts
+    std::vector<int32_t> bounds(m + 1);
+    {
+        int32_t row = 0;
+        for (int i = 0; i <= m; i++) {
+            rc = cudaMemcpyAsync(&bounds[i], C->rowptr + row, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream) == cudaSuccess
+                     ? BSP_OK : BSP_ERR_CUDA;
+            if (rc != BSP_OK) break;
+            if (i < m) row += as[i]->nbr;
+        }
+        if (rc == BSP_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = BSP_ERR_CUDA;
+    }
+    int32_t row = 0;
+    for (int i = 0; i < m && rc == BSP_OK; i++) {
+        bsp_mat *P = nullptr;
+        rc = new_empty_like(ctx, as[i]->rows, bs[i]->cols, k, as[i]->nbr, bs[i]->nbc, &P, esize);
+        if (rc == BSP_OK) rc = fill(P, bounds[i + 1] - bounds[i]);
+        if (rc == BSP_OK) rc = bsp_split_rows_device(ctx, C, row, bounds[i], P);
+        if (rc != BSP_OK) { bsp_mat_free(ctx, P); break; }
+        cs->push_back(P);
+        row += as[i]->nbr;
+    }
+    bsp_mat_free(ctx, C);
+    if (rc != BSP_OK) {
+        if (rc == BSP_ERR_CUDA) snprintf(ctx->err, sizeof(ctx->err), "batched chain level: CUDA copy failed");
+        for (auto *p : *cs) bsp_mat_free(ctx, p);
+        cs->clear();
+    }
+    return rc;
+}
+
 } // namespace
 
 extern "C" {
@@ -146,6 +212,8 @@ int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
         ctx->force_generic = fg && fg[0] == '1';
         const char *tr = getenv("BSP_TRACE");
         ctx->trace = tr && tr[0] == '1';
+        const char *nb = getenv("BSP_NO_BATCH");
+        ctx->no_batch = nb && nb[0] == '1';
     }
     // keep freed blocks in the stream-ordered pool: a chain allocates and frees every product
     cudaMemPool_t pool;
@@ -439,10 +507,34 @@ int bsp_chain(bsp_ctx *ctx, bsp_mat *const *mats, int32_t n, bsp_mat **out, bsp_
         const size_t len = cur.size();
         std::vector<bsp_mat *> nxt;
         std::vector<char> nxt_owned;
-        for (size_t ind = 0; ind + 1 < len; ind += 2) { // cu:297: adjacent pairs
+        for (size_t ind = 0; ind + 1 < len; ind += 2) // cu:297: adjacent pairs; cu:301: the reference's log line
             if (log && lp + 48 < log_cap)
                 lp += (size_t)snprintf(log + lp, log_cap - lp, "multiplying %d %d\n", log_base + (int)ind,
-                                       log_base + (int)ind + 1); // cu:301
+                                       log_base + (int)ind + 1);
+        // several small products on one level: run them as one stacked product
+        const size_t npairs = len / 2;
+        int64_t level_tiles = 0;
+        bool same = true;
+        for (size_t ind = 0; ind + 1 < len; ind += 2) {
+            level_tiles += cur[ind]->nnzb + cur[ind + 1]->nnzb;
+            same = same && cur[ind]->k == cur[0]->k && cur[ind + 1]->k == cur[0]->k &&
+                   cur[ind]->esize == cur[0]->esize && cur[ind + 1]->esize == cur[0]->esize;
+        }
+        if (!ctx->no_batch && same && npairs >= 2 && level_tiles <= (int64_t)4 << 20) {
+            std::vector<bsp_mat *> as, bs, cs;
+            for (size_t ind = 0; ind + 1 < len; ind += 2) { as.push_back(cur[ind]); bs.push_back(cur[ind + 1]); }
+            bsp_stats st;
+            rc = batched_level(ctx, as, bs, &cs, &st);
+            if (rc == BSP_OK) {
+                accumulate(&tot, st);
+                for (auto *c : cs) { nxt.push_back(c); nxt_owned.push_back(1); }
+                for (size_t ind = 0; ind + 1 < len; ind += 2) {
+                    if (owned[ind]) { bsp_mat_free(ctx, cur[ind]); cur[ind] = nullptr; }
+                    if (owned[ind + 1]) { bsp_mat_free(ctx, cur[ind + 1]); cur[ind + 1] = nullptr; }
+                }
+            }
+        } else
+        for (size_t ind = 0; ind + 1 < len; ind += 2) {
             bsp_mat *c = nullptr;
             bsp_stats st;
             rc = bsp_spgemm(ctx, cur[ind], cur[ind + 1], &c, &st);

@@ -28,6 +28,7 @@ struct bsp_ctx {
     void *d_counters;    // 256 B of device counters (exact-refold count of the numeric pass)
     bool force_generic;  // BSP_FORCE_GENERIC=1: always use the any-k exact numeric kernel (tests)
     int f32_path;        // float32 products: 0 = auto (tensor cores for k = 32 / 64), 1 = SIMT, 2 = tensor cores
+    bool no_batch;       // BSP_NO_BATCH=1: a chain level is never run as one stacked product (tests, comparisons)
     bool trace;          // BSP_TRACE=1: per-sub-phase device timings of every product on stderr
     int ntrace;
     cudaEvent_t trace_ev[32];
@@ -166,6 +167,9 @@ int bsp_numeric(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
 
 int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m);
 int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_mat *out);
+int bsp_stack_rows_device(bsp_ctx *ctx, const bsp_mat *const *mats, int n, const int32_t *shifts, const int32_t *limits,
+                          int32_t sentinel, bsp_mat *out);
+int bsp_split_rows_device(bsp_ctx *ctx, const bsp_mat *big, int32_t row_off, int64_t tile_off, bsp_mat *part);
 int bsp_expand_rows(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_brow);
 int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t esize, int64_t nnzb,
                    const int32_t *d_brow, const int32_t *d_bcol, const void *d_vals,

@@ -256,3 +256,79 @@ int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bs
     }
     return BSP_OK;
 }
+
+// ---- batching of independent products (one tree level of a chain) ------------------------------
+// C_i = A_i * B_i for i = 0..m-1 equals the vertical stack of the C_i when the A_i are stacked
+// with their column indices shifted by the row offset of B_i in the stack of the B_i:
+//     [A_0 (cols + 0); A_1 (cols + nbr(B_0)); ...] * [B_0; B_1; ...] = [C_0; C_1; ...]
+// Column indices of B (and C) stay local, so the symbolic bitmaps keep their width; every pair
+// list is the same as in the separate product.  A column index that has no partner row in its
+// own B_i is replaced by a sentinel beyond the stacked B so that it cannot hit B_{i+1}.
+namespace {
+
+__global__ void stack_rowptr_kernel(const int32_t *__restrict__ src, int32_t n_rows, int32_t tile_off,
+                                    int32_t *__restrict__ dst /* already offset to this block's first row */, int last)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < n_rows + (last ? 1 : 0)) dst[r] = src[r] + tile_off;
+}
+
+__global__ void stack_colidx_kernel(const int32_t *__restrict__ src, int64_t n, int32_t shift, int32_t limit,
+                                    int32_t sentinel, int32_t *__restrict__ dst)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const int32_t j = src[i];
+        dst[i] = (limit >= 0 && j >= limit) ? sentinel : j + shift;
+    }
+}
+
+__global__ void split_rowptr_kernel(const int32_t *__restrict__ src /* at the block's first row */, int32_t n_rows,
+                                    int32_t tile_off, int32_t *__restrict__ dst)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r <= n_rows) dst[r] = src[r] - tile_off;
+}
+
+} // namespace
+
+// shifts / limits may be null (no column shift: used for the B side)
+int bsp_stack_rows_device(bsp_ctx *ctx, const bsp_mat *const *mats, int n, const int32_t *shifts, const int32_t *limits,
+                          int32_t sentinel, bsp_mat *out /* arrays allocated, nbr / nnzb set */)
+{
+    const size_t tb = (size_t)out->k * out->k * out->esize;
+    int64_t tile_off = 0;
+    int32_t row_off = 0;
+    for (int i = 0; i < n; i++) {
+        const bsp_mat *m = mats[i];
+        stack_rowptr_kernel<<<blocks_for((int64_t)m->nbr + 1, 256), 256, 0, ctx->stream>>>(
+            m->rowptr, m->nbr, (int32_t)tile_off, out->rowptr + row_off, i == n - 1);
+        BSP_LAUNCH_CHECK(ctx);
+        if (m->nnzb) {
+            stack_colidx_kernel<<<blocks_for(m->nnzb, 256), 256, 0, ctx->stream>>>(
+                m->colidx, m->nnzb, shifts ? shifts[i] : 0, limits ? limits[i] : -1, sentinel, out->colidx + tile_off);
+            BSP_LAUNCH_CHECK(ctx);
+            BSP_CUDA(ctx, cudaMemcpyAsync((char *)out->vals + (size_t)tile_off * tb, m->vals, (size_t)m->nnzb * tb,
+                                          cudaMemcpyDeviceToDevice, ctx->stream));
+        }
+        tile_off += m->nnzb;
+        row_off += m->nbr;
+    }
+    if (n == 0) BSP_CUDA(ctx, cudaMemsetAsync(out->rowptr, 0, sizeof(int32_t), ctx->stream));
+    return BSP_OK;
+}
+
+// block rows [row_off, row_off + part->nbr) of `big` -> part (arrays allocated by the caller from tile counts)
+int bsp_split_rows_device(bsp_ctx *ctx, const bsp_mat *big, int32_t row_off, int64_t tile_off, bsp_mat *part)
+{
+    const size_t tb = (size_t)big->k * big->k * big->esize;
+    split_rowptr_kernel<<<blocks_for((int64_t)part->nbr + 1, 256), 256, 0, ctx->stream>>>(big->rowptr + row_off, part->nbr,
+                                                                                           (int32_t)tile_off, part->rowptr);
+    BSP_LAUNCH_CHECK(ctx);
+    if (part->nnzb) {
+        BSP_CUDA(ctx, cudaMemcpyAsync(part->colidx, big->colidx + tile_off, (size_t)part->nnzb * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        BSP_CUDA(ctx, cudaMemcpyAsync(part->vals, (const char *)big->vals + (size_t)tile_off * tb, (size_t)part->nnzb * tb,
+                                      cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    return BSP_OK;
+}

@@ -352,3 +352,34 @@ def test_text_io_roundtrip_large(ctx):
         with pytest.raises(bspgemm.BspError) as e:
             ctx.read_text(p, k)
         assert e.value.code == 5
+
+
+def test_chain_levels_run_as_stacked_products(ctx):
+    """A tree level with several small products is executed as one stacked product
+    (BSP_NO_BATCH=1 turns that off): rectangular factors of different sizes, inner indices
+    without partner rows, empty factors -- all must equal the oracle and the unbatched run."""
+    import os
+    k = 4
+    dims = [10, 14, 9, 20, 6, 11, 11, 3, 17, 8, 12]   # factor i is dims[i] x dims[i+1] blocks
+    host = []
+    for i in range(len(dims) - 1):
+        dens = 0.0 if i == 6 else 0.45                  # factor 6 is empty
+        m = bsp_gen.random_matrix(dims[i] * k, dims[i + 1] * k, k, dens, 600 + i, "edgy")
+        host.append(m)
+    # an A column index beyond its partner's last block row
+    r, c, kk, br, bc, v = host[2]
+    host[2] = (r, c, kk, np.append(br, 0).astype(np.int32), np.append(bc, 500).astype(np.int32),
+               np.concatenate([v, np.ones((1, k, k), np.uint64)]))
+    ref = orc.chain([orc.OMat.from_coo(*m) for m in host])[0]
+    st = bspgemm.Stats()
+    res = ctx.helper2([dev(ctx, m) for m in host], stats=st)
+    assert_same(res, ref)
+    try:
+        os.environ["BSP_NO_BATCH"] = "1"
+        with bspgemm.Context(0) as c2:
+            st2 = bspgemm.Stats()
+            res2 = c2.helper2([c2.matrix_from_coo(*m) for m in host], stats=st2)
+            assert_same(res2, ref)
+            assert st2.nprod == st.nprod and st2.launches > st.launches
+    finally:
+        os.environ.pop("BSP_NO_BATCH", None)
