@@ -529,21 +529,110 @@ sym_fill_global_kernel(const int32_t *__restrict__ rowlist, const int32_t *__res
     }
 }
 
+// ---- fill, tiny rows: one WARP per block row, no bitmap ------------------------------------------
+// A row with at most TINY_P tile products and TINY_A entries in its A row is sorted instead of
+// bit-mapped: every product gets the key (block column << 5 | ordinal of its A entry); a bitonic
+// sort of the <= 256 keys in shared memory groups the products by output tile with ascending j
+// inside a tile, which IS the pair list; tile heads are found with a ballot, their ranks with
+// a popcount prefix.  This is the common case of chain levels with few factors, of most R-MAT
+// rows and of small inputs, where a 512-thread CTA per row mostly waits at barriers.
+constexpr int TINY_P = 256;
+constexpr int TINY_A = 32;
+constexpr int TINY_WARPS = 8;
+
+__global__ void __launch_bounds__(TINY_WARPS * 32)
+sym_fill_tiny_kernel(const int32_t *__restrict__ rowlist, int nrows, const int32_t *__restrict__ a_rowptr,
+                     const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
+                     const int32_t *__restrict__ b_colidx, const int32_t *__restrict__ c_rowptr,
+                     const int64_t *__restrict__ row_prod_ptr, int32_t *__restrict__ c_colidx,
+                     int64_t *__restrict__ pair_ptr, int2 *__restrict__ pairs)
+{
+    __shared__ uint32_t keys_sh[TINY_WARPS][TINY_P];
+    __shared__ int32_t vals_sh[TINY_WARPS][TINY_P];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t *keys = keys_sh[warp];
+    int32_t *vals = vals_sh[warp];
+    for (int li = blockIdx.x * TINY_WARPS + warp; li < nrows; li += gridDim.x * TINY_WARPS) {
+        const int row = rowlist[li];
+        const int cbase = c_rowptr[row];
+        const int64_t pbase = row_prod_ptr[row];
+        const int P = (int)(row_prod_ptr[row + 1] - pbase);
+        const int a0 = a_rowptr[row], nA = a_rowptr[row + 1] - a0;
+        // lane e holds A entry e: first B tile and number of products
+        int b0 = 0, len = 0;
+        if (lane < nA) {
+            const int j = a_colidx[a0 + lane];
+            if (j < b_nbr) { b0 = b_rowptr[j]; len = b_rowptr[j + 1] - b0; }
+        }
+        int tot;
+        const int off = warp_excl_scan(len, &tot);
+        // keys: (block column, A entry ordinal); values: index of the B tile
+        for (int e = 0; e < nA; e++) {
+            const int eb0 = __shfl_sync(0xffffffffu, b0, e), elen = __shfl_sync(0xffffffffu, len, e);
+            const int eoff = __shfl_sync(0xffffffffu, off, e);
+            for (int i = lane; i < elen; i += 32) {
+                keys[eoff + i] = ((uint32_t)b_colidx[eb0 + i] << 5) | (uint32_t)e;
+                vals[eoff + i] = eb0 + i;
+            }
+        }
+        int N = 32;
+        while (N < P) N <<= 1;
+        for (int x = P + lane; x < N; x += 32) keys[x] = 0xffffffffu;
+        __syncwarp();
+        // bitonic sort of N (<= 256) keys with their values
+        for (int size = 2; size <= N; size <<= 1) {
+            for (int stride = size >> 1; stride > 0; stride >>= 1) {
+                for (int x = lane; x < N / 2; x += 32) {
+                    const int lo = ((x / stride) * stride * 2) + (x % stride), hi = lo + stride;
+                    const bool up = ((lo & size) == 0);
+                    const uint32_t k0 = keys[lo], k1 = keys[hi];
+                    if ((k0 > k1) == up) {
+                        keys[lo] = k1; keys[hi] = k0;
+                        const int32_t v0 = vals[lo];
+                        vals[lo] = vals[hi]; vals[hi] = v0;
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        // tile heads, ranks, outputs
+        int tiles_before = 0;
+        for (int x0 = 0; x0 < P; x0 += 32) {
+            const int x = x0 + lane;
+            const bool in = x < P;
+            const uint32_t key = in ? keys[x] : 0xffffffffu;
+            const bool head = in && (x == 0 || (keys[x - 1] >> 5) != (key >> 5));
+            const bool last = in && (x == P - 1 || (keys[x + 1] >> 5) != (key >> 5));
+            const unsigned hm = __ballot_sync(0xffffffffu, head);
+            if (head) {
+                const int t = tiles_before + __popc(hm & ((1u << lane) - 1u));
+                c_colidx[cbase + t] = (int32_t)(key >> 5);
+                pair_ptr[(size_t)cbase + t] = pbase + x;
+            }
+            if (in) pairs[pbase + x] = make_int2(a0 + (int)(key & 31u), vals[x] | (last ? (int)0x80000000 : 0));
+            tiles_before += __popc(hm);
+        }
+        __syncwarp();
+    }
+}
+
 // ---- rows -> capacity classes -----------------------------------------------------------------
 // class c rows go to lists[c * nbr ...]; counts[c] = rows in class c.  A row with P tile
 // products fits class c when P <= caps[c]; larger than every cap -> class NCLASS-1 (global).
-constexpr int NCLASS = 4;
+constexpr int NCLASS = 5; // 0: tiny rows (warp + sort), 1..3: shared-memory CTA classes, 4: global-memory CTA
 
 __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowptr,
                                      const int32_t *__restrict__ row_cnt, const int32_t *__restrict__ row_prod,
                                      int cap0, int cap1, int cap2, int tcap0, int tcap1, int tcap2, int acap,
-                                     int32_t *__restrict__ lists, int32_t *__restrict__ counts)
+                                     int tiny_ok, int32_t *__restrict__ lists, int32_t *__restrict__ counts)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nbr || row_cnt[row] == 0) return;
     const int P = row_prod[row], T = row_cnt[row];
-    int cls = (P <= cap0 && T <= tcap0) ? 0 : ((P <= cap1 && T <= tcap1) ? 1 : ((P <= cap2 && T <= tcap2) ? 2 : 3));
-    if (a_rowptr[row + 1] - a_rowptr[row] > acap) cls = 3; // A row too long for the shared-memory entry table
+    const int nA = a_rowptr[row + 1] - a_rowptr[row];
+    int cls = (P <= cap0 && T <= tcap0) ? 1 : ((P <= cap1 && T <= tcap1) ? 2 : ((P <= cap2 && T <= tcap2) ? 3 : 4));
+    if (nA > acap) cls = 4;                                  // A row too long for the shared-memory entry table
+    if (tiny_ok && P <= TINY_P && nA <= TINY_A) cls = 0;     // warp-per-row sort
     const int slot = atomicAdd(&counts[cls], 1);
     lists[(size_t)cls * nbr + slot] = row;
 }
@@ -592,6 +681,8 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
             caps[0] = tcaps[0] = a; caps[1] = tcaps[1] = b; caps[2] = tcaps[2] = c;
         }
     }
+    // the tiny-row kernel packs the block column into 27 bits; BSP_SYM_CAPS (a test hook) also switches it off
+    const int tiny_ok = (B->nbc < (1 << 27) && !getenv("BSP_SYM_CAPS")) ? 1 : 0;
     for (int c = 0; c < 3; c++) {
         if (caps[c] > 60000) caps[c] = 60000; // tile ranks are kept as 16-bit values in shared memory
         if (tcaps[c] > caps[c]) tcaps[c] = caps[c];
@@ -618,7 +709,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         }
         classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, A->rowptr, row_cnt, row_prod, caps[0],
                                                                         caps[1], caps[2], tcaps[0], tcaps[1], tcaps[2],
-                                                                        acap, lists, counts);
+                                                                        acap, tiny_ok, lists, counts);
         BSP_LAUNCH_CHECK(ctx);
     }
     bsp_trace_mark(ctx, "sym_count");
@@ -647,20 +738,28 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     BSP_CUDA(ctx, cudaMemcpyAsync(out->pair_ptr + out->nnzb_c, row_prod_ptr + nbr, sizeof(int64_t),
                                   cudaMemcpyDeviceToDevice, ctx->stream));
     bsp_trace_mark(ctx, "sym_sync_alloc");
+    if (ncls[0] > 0) {
+        int g = (ncls[0] + TINY_WARPS - 1) / TINY_WARPS;
+        if (g > ctx->sm_count * 16) g = ctx->sm_count * 16;
+        sym_fill_tiny_kernel<<<g, TINY_WARPS * 32, 0, ctx->stream>>>(lists, ncls[0], A->rowptr, A->colidx, B->nbr, B->rowptr,
+                                                                    B->colidx, out->c_rowptr, row_prod_ptr, out->c_colidx,
+                                                                    out->pair_ptr, out->pairs);
+        BSP_LAUNCH_CHECK(ctx);
+    }
     for (int c = 0; c < 3; c++) {
-        if (ncls[c] == 0) continue;
+        if (ncls[c + 1] == 0) continue;
         const size_t bytes = fill_smem_bytes(words, caps[c], tcaps[c], acap);
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        sym_fill_smem_kernel<<<ncls[c], FILL_THREADS, bytes, ctx->stream>>>(
-            lists + (size_t)c * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, caps[c], tcaps[c], acap,
+        sym_fill_smem_kernel<<<ncls[c + 1], FILL_THREADS, bytes, ctx->stream>>>(
+            lists + (size_t)(c + 1) * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, caps[c], tcaps[c], acap,
             out->c_rowptr, row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
-    if (ncls[3] > 0) {
+    if (ncls[4] > 0) {
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)bitmap_bytes));
-        sym_fill_global_kernel<<<ncls[3], FILLG_THREADS, bitmap_bytes, ctx->stream>>>(
-            lists + (size_t)3 * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, out->c_rowptr,
+        sym_fill_global_kernel<<<ncls[4], FILLG_THREADS, bitmap_bytes, ctx->stream>>>(
+            lists + (size_t)4 * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, out->c_rowptr,
             row_prod_ptr, out->c_colidx, (unsigned long long *)out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
