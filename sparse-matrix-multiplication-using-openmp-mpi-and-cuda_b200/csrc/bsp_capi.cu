@@ -1,4 +1,6 @@
 // bsp_capi.cu -- the extern "C" boundary declared in include/bspgemm.h.
+#include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <new>
 #include <vector>
@@ -202,6 +204,7 @@ int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
         ctx->owns_stream = true;
     }
     for (int i = 0; i < 4; i++) BSP_CUDA(ctx, cudaEventCreate(&ctx->ev[i]));
+    BSP_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)); // downloads overlapped with compute
     ctx->pinned_bytes = 4096;
     BSP_CUDA(ctx, cudaMallocHost(&ctx->pinned, ctx->pinned_bytes));
     memset(ctx->pinned, 0, ctx->pinned_bytes);
@@ -233,6 +236,7 @@ void bsp_ctx_destroy(bsp_ctx *ctx)
         if (ctx->trace_ev[i]) cudaEventDestroy(ctx->trace_ev[i]);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     if (ctx->d_counters) cudaFree(ctx->d_counters);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->owns_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -580,20 +584,92 @@ int bsp_multiply_host(bsp_ctx *ctx, int32_t k, int32_t rows_a, int32_t cols_a, i
     bsp_mat *A = nullptr, *B = nullptr, *C = nullptr;
     int rc = bsp_mat_from_coo(ctx, rows_a, cols_a, k, nnzb_a, brow_a, bcol_a, vals_a, &A);
     if (rc == BSP_OK) rc = bsp_mat_from_coo(ctx, rows_b, cols_b, k, nnzb_b, brow_b, bcol_b, vals_b, &B);
-    if (rc == BSP_OK) rc = bsp_spgemm(ctx, A, B, &C, stats);
+    const bool want_out = brow_c || bcol_c || vals_c;
+    const char *nopipe = getenv("BSP_NO_PIPELINE");
+    auto now_ms = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_start = now_ms();
+    if (rc == BSP_OK && (!want_out || A->nnzb < 65536 || !ctx->copy_stream || (nopipe && nopipe[0] == '1'))) {
+        // small problem or size query: one product, one download
+        rc = bsp_spgemm(ctx, A, B, &C, stats);
+        if (rc == BSP_OK) {
+            *nnzb_c = C->nnzb;
+            if (want_out) {
+                if (C->nnzb > cap_c) {
+                    snprintf(ctx->err, sizeof(ctx->err), "bsp_multiply_host: result has %lld tiles, capacity %lld",
+                             (long long)C->nnzb, (long long)cap_c);
+                    rc = BSP_ERR_LIMIT;
+                } else {
+                    rc = bsp_mat_to_coo(ctx, C, brow_c, bcol_c, vals_c);
+                }
+            }
+        }
+        bsp_mat_free(ctx, A); bsp_mat_free(ctx, B); bsp_mat_free(ctx, C);
+        return rc;
+    }
+    // Large result: the download (PCIe, ~50 GB/s) dwarfs the product.  Compute block-row panels
+    // one after the other and download panel p on a second stream while panel p+1 is computed.
+    constexpr int NP = 8;
+    bsp_mat *panels[NP] = {};
+    int32_t *d_brow[NP] = {};
+    bsp_stats tot;
+    memset(&tot, 0, sizeof(tot));
+    int64_t done = 0;
     if (rc == BSP_OK) {
-        *nnzb_c = C->nnzb;
-        if (brow_c || bcol_c || vals_c) {
-            if (C->nnzb > cap_c) {
-                snprintf(ctx->err, sizeof(ctx->err), "bsp_multiply_host: result has %lld tiles, capacity %lld",
-                         (long long)C->nnzb, (long long)cap_c);
+        // panel bounds: equal shares of A's tiles (host histogram of the caller's coordinates)
+        std::vector<int64_t> cnt((size_t)A->nbr + 1, 0);
+        for (int64_t i = 0; i < nnzb_a; i++) cnt[(size_t)brow_a[i] + 1]++;
+        for (int32_t r = 0; r < A->nbr; r++) cnt[(size_t)r + 1] += cnt[(size_t)r];
+        int32_t lo = 0;
+        const size_t tb = (size_t)k * k * sizeof(uint64_t);
+        for (int p = 0; p < NP && rc == BSP_OK; p++) {
+            int32_t hi = A->nbr;
+            if (p + 1 < NP) {
+                const int64_t target = nnzb_a * (p + 1) / NP;
+                hi = (int32_t)(std::lower_bound(cnt.begin(), cnt.end(), target) - cnt.begin());
+                if (hi < lo) hi = lo;
+                if (hi > A->nbr) hi = A->nbr;
+            }
+            bsp_stats st;
+            rc = spgemm_impl(ctx, A, B, lo, hi, &panels[p], &st);
+            lo = hi;
+            if (rc != BSP_OK) break;
+            accumulate(&tot, st);
+            bsp_mat *P = panels[p];
+            if (done + P->nnzb > cap_c) {
+                snprintf(ctx->err, sizeof(ctx->err), "bsp_multiply_host: result has more than %lld tiles (capacity)", (long long)cap_c);
                 rc = BSP_ERR_LIMIT;
-            } else {
-                rc = bsp_mat_to_coo(ctx, C, brow_c, bcol_c, vals_c);
+                break;
+            }
+            if (P->nnzb) {
+                rc = bsp_alloc(ctx, &d_brow[p], (size_t)P->nnzb);
+                if (rc == BSP_OK) rc = bsp_expand_rows(ctx, P, d_brow[p]);
+                if (rc != BSP_OK) break;
+                // copy stream waits for this panel, then downloads it while the next panel is computed
+                cudaEventRecord(ctx->ev[3], ctx->stream);
+                cudaStreamWaitEvent(ctx->copy_stream, ctx->ev[3], 0);
+                if (brow_c) cudaMemcpyAsync(brow_c + done, d_brow[p], (size_t)P->nnzb * 4, cudaMemcpyDeviceToHost, ctx->copy_stream);
+                if (bcol_c) cudaMemcpyAsync(bcol_c + done, P->colidx, (size_t)P->nnzb * 4, cudaMemcpyDeviceToHost, ctx->copy_stream);
+                if (vals_c) cudaMemcpyAsync((char *)vals_c + (size_t)done * tb, P->vals, (size_t)P->nnzb * tb, cudaMemcpyDeviceToHost, ctx->copy_stream);
+                done += P->nnzb;
             }
         }
     }
-    bsp_mat_free(ctx, A); bsp_mat_free(ctx, B); bsp_mat_free(ctx, C);
+    const double t_panels = now_ms();
+    if (ctx->copy_stream && cudaStreamSynchronize(ctx->copy_stream) != cudaSuccess && rc == BSP_OK) {
+        snprintf(ctx->err, sizeof(ctx->err), "bsp_multiply_host: download failed: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = BSP_ERR_CUDA;
+    }
+    const double t_copied = now_ms();
+    for (int p = 0; p < NP; p++) { bsp_release(ctx, d_brow[p]); bsp_mat_free(ctx, panels[p]); }
+    bsp_mat_free(ctx, A); bsp_mat_free(ctx, B);
+    if (ctx->trace)
+        fprintf(stderr, "[bsp trace] multiply_host: panels issued after %.1f ms, downloads done after %.1f ms\n",
+                t_panels - t_start, t_copied - t_start);
+    if (rc == BSP_OK) {
+        *nnzb_c = done;
+        tot.nnzb_a = nnzb_a; tot.nnzb_b = B ? tot.nnzb_b / NP : 0;
+        if (stats) *stats = tot;
+    }
     return rc;
 }
 

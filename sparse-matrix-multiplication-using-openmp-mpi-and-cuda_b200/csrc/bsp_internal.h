@@ -19,6 +19,7 @@
 struct bsp_ctx {
     int device;
     cudaStream_t stream;
+    cudaStream_t copy_stream; // second stream: device->host copies of bsp_multiply_host overlap the next panel
     bool owns_stream;
     int sm_count;
     int64_t launches;

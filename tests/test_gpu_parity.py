@@ -383,3 +383,18 @@ def test_chain_levels_run_as_stacked_products(ctx):
             assert st2.nprod == st.nprod and st2.launches > st.launches
     finally:
         os.environ.pop("BSP_NO_BATCH", None)
+
+
+def test_multiply_host_pipelined_download(ctx):
+    """Above 65536 tiles in A the host-to-host call computes block-row panels and downloads one
+    while the next is computed; the concatenated result must be the sorted product."""
+    k, G = 4, 2048
+    a = bsp_gen.random_matrix(G * k, G * k, k, 0.02, 41, "u64")
+    b = bsp_gen.random_matrix(G * k, G * k, k, 0.004, 42, "u64")
+    assert a[3].size >= 65536
+    st = bspgemm.Stats()
+    br, bc, v = ctx.multiply_host(k, (a[0], a[1], a[3], a[4], a[5]), (b[0], b[1], b[3], b[4], b[5]), stats=st)
+    ref, nprod = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b), threads=8)
+    rbr, rbc, rv = ref.coo()
+    assert st.nprod == nprod and st.nnzb_c == ref.nnzb
+    assert np.array_equal(br, rbr) and np.array_equal(bc, rbc) and np.array_equal(v, rv)
