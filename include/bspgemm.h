@@ -193,6 +193,30 @@ int bsp_mat_read_text(bsp_ctx *ctx, const char *path, int32_t k, bsp_mat **out);
  * values, single spaces, no trailing space, '\n' line ends), tiles in (brow, bcol) order. */
 int bsp_mat_write_text(bsp_ctx *ctx, const bsp_mat *m, const char *path);
 
+/* Parse n files at once: host threads parse into pinned staging buffers while the calling
+ * thread uploads (asynchronous copies) and builds the finished ones on the device, so upload
+ * and ingestion hide behind parsing.  The reference loads its files with one OpenMP task per
+ * file into pageable memory (cu:334-339); the pinned/asynchronous ingestion its report
+ * describes is not in its code.  out[i] receives the matrix of paths[i]; on error every out[i]
+ * is NULL and nothing is left allocated. */
+int bsp_mat_read_text_many(bsp_ctx *ctx, const char *const *paths, int32_t n, int32_t k, bsp_mat **out);
+
+/* ---- binary container + content checksum (no counterpart in the reference) ------------ */
+
+/* 64-bit checksum of the matrix content (header, tile coordinates, tile values), computed on
+ * the device in one pass over the tiles.  It depends on the content only, not on how the
+ * matrix was produced (one GPU or row panels on several), so full-size results -- 19.5 GB for
+ * BASELINE.json configs[1], where the reference's only comparison is a diff of 35-50 GB text
+ * files (cu:595-608) -- can be compared by value.  Defined in csrc/bsp_checksum.cu. */
+int bsp_mat_checksum(bsp_ctx *ctx, const bsp_mat *m, uint64_t *out);
+
+/* Binary file: 64-byte header ("BSPMAT01", rows, cols, k, element size, tile count, checksum),
+ * then brow[], bcol[] (int32, tiles in (brow, bcol) order) and the tile values.  The reader
+ * verifies the checksum on the device and returns BSP_ERR_IO on a mismatch.  Works for uint64
+ * and float32 matrices. */
+int bsp_mat_write_bin(bsp_ctx *ctx, const bsp_mat *m, const char *path);
+int bsp_mat_read_bin(bsp_ctx *ctx, const char *path, bsp_mat **out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,6 +9,9 @@
 #      collect-then-erase                                          ("fixed" variants only)
 #   3. cu:162,179,224,241,256,273  the reference's own commented-out phase-timer prints are
 #      re-enabled                                                  ("timed" variant only)
+#   4. (ref_gpu only) no launch edit at all: the translation unit is compiled by nvcc for sm_100a with the
+#      real CUDA runtime (edits 2+3 only), i.e. the reference's own kernel and host packing on the
+#      same B200 -- SURVEY.md 8(d) "Reference GPU build on B200", a second reported comparator.
 # Variants: ref_host (1), ref_host_fixed (1+2), ref_host_timed (1+2+3, OpenMP block loop off),
 #           ref_host_timed_omp (1+2+3 and the emulated launch spread over OpenMP threads).
 set -euo pipefail
@@ -34,5 +37,13 @@ $CXX $flags "$out/ref_host.cpp" -o "$out/ref_host"
 $CXX $flags "$out/ref_host_fixed.cpp" -o "$out/ref_host_fixed"
 $CXX $flags "$out/ref_host_timed.cpp" -o "$out/ref_host_timed"
 $CXX $flags -DSHIM_OMP_LAUNCH "$out/ref_host_timed.cpp" -o "$out/ref_host_timed_omp"
+if command -v nvcc >/dev/null 2>&1; then
+  # the shim directory also holds the cuda_runtime.h stand-in, which must NOT be seen by nvcc
+  mkdir -p "$out/mpi_only" && cp "$here/shim/mpi.h" "$out/mpi_only/mpi.h"
+  sed -e "$fix" -e "$timers" "$src" > "$out/ref_gpu.cu"
+  nvcc -O3 -gencode arch=compute_100a,code=sm_100a -I"$out/mpi_only" -Xcompiler -fopenmp -ccbin "$CXX" -w \
+       "$out/ref_gpu.cu" -o "$out/ref_gpu"
+  rm -rf "$out/ref_gpu.cu" "$out/mpi_only"
+fi
 rm -f "$out"/*.cpp
 echo "build_ref: built $(ls "$out" | tr '\n' ' ')"

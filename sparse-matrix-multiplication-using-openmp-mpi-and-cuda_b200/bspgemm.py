@@ -73,6 +73,10 @@ _SIGNATURES = {
                                          C.POINTER(C.c_int64)]),
     "bsp_mat_read_text": (C.c_int, [_VP, C.c_char_p, C.c_int32, C.POINTER(_VP)]),
     "bsp_mat_write_text": (C.c_int, [_VP, _VP, C.c_char_p]),
+    "bsp_mat_read_text_many": (C.c_int, [_VP, C.POINTER(C.c_char_p), C.c_int32, C.c_int32, C.POINTER(_VP)]),
+    "bsp_mat_checksum": (C.c_int, [_VP, _VP, C.POINTER(C.c_uint64)]),
+    "bsp_mat_write_bin": (C.c_int, [_VP, _VP, C.c_char_p]),
+    "bsp_mat_read_bin": (C.c_int, [_VP, C.c_char_p, C.POINTER(_VP)]),
 }
 
 _lib = None
@@ -167,6 +171,15 @@ class Matrix:
     def write_text(self, path):
         self.ctx._ck(self.ctx.lib.bsp_mat_write_text(self.ctx.handle, self.handle, os.fsencode(path)))
 
+    def write_bin(self, path):
+        self.ctx._ck(self.ctx.lib.bsp_mat_write_bin(self.ctx.handle, self.handle, os.fsencode(path)))
+
+    def checksum(self):
+        """64-bit content checksum computed on the device (csrc/bsp_checksum.cu)."""
+        v = C.c_uint64()
+        self.ctx._ck(self.ctx.lib.bsp_mat_checksum(self.ctx.handle, self.handle, C.byref(v)))
+        return v.value
+
 
 class Context:
     """One device + one stream (replaces the staging buffers main lends to helper, cu:421-436)."""
@@ -243,6 +256,19 @@ class Context:
     def read_text(self, path, k):
         h = _VP()
         self._ck(self.lib.bsp_mat_read_text(self.handle, os.fsencode(path), k, C.byref(h)))
+        return Matrix(self, h.value)
+
+    def read_text_many(self, paths, k):
+        """Parse several files with upload/ingestion overlapped with parsing; list of Matrix."""
+        n = len(paths)
+        arr = (C.c_char_p * n)(*[os.fsencode(p) for p in paths])
+        hs = (_VP * n)()
+        self._ck(self.lib.bsp_mat_read_text_many(self.handle, arr, n, k, hs))
+        return [Matrix(self, hs[i]) for i in range(n)]
+
+    def read_bin(self, path):
+        h = _VP()
+        self._ck(self.lib.bsp_mat_read_bin(self.handle, os.fsencode(path), C.byref(h)))
         return Matrix(self, h.value)
 
     # ---- the hot path -----------------------------------------------------------------------

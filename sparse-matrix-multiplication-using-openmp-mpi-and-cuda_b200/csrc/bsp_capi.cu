@@ -52,8 +52,29 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     BSP_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
     bsp_trace_mark(ctx, "start");
     bsp_symbolic_out sym;
+    memset(&sym, 0, sizeof(sym));
+    sym.pair_budget = ctx->pair_budget;
     int rc = bsp_symbolic(ctx, A, B, row_lo, row_hi, &sym);
     if (rc != BSP_OK) { delete c; return rc; }
+    if (sym.n_split > 0) {
+        // The pair lists (8 B per tile product) of this product do not fit the budget: compute it in
+        // row panels whose lists do and put the panels together.  Rows are independent and every
+        // output element keeps its accumulation order, so the result is the same bit for bit.
+        delete c;
+        std::vector<bsp_mat *> parts((size_t)sym.n_split, nullptr);
+        for (int p = 0; p < sym.n_split && rc == BSP_OK; p++) {
+            bsp_stats ps;
+            rc = spgemm_impl(ctx, A, B, sym.split[p], sym.split[p + 1], &parts[(size_t)p], &ps);
+            if (rc == BSP_OK) { const int64_t na = st.nnzb_a, nb = st.nnzb_b; accumulate(&st, ps); st.nnzb_a = na; st.nnzb_b = nb; }
+        }
+        free(sym.split);
+        if (rc == BSP_OK) rc = bsp_mat_concat_panels(ctx, parts.data(), (int32_t)parts.size(), C);
+        for (auto *m : parts) bsp_mat_free(ctx, m);
+        if (rc != BSP_OK) { bsp_mat_free(ctx, *C); *C = nullptr; return rc; }
+        st.launches = ctx->launches - launches0;
+        if (stats) *stats = st;
+        return BSP_OK;
+    }
     c->rowptr = sym.c_rowptr; // from here on bsp_mat_free(c) releases the pattern arrays
     c->colidx = sym.c_colidx;
     c->nnzb = sym.nnzb_c;
@@ -217,6 +238,12 @@ int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
         ctx->trace = tr && tr[0] == '1';
         const char *nb = getenv("BSP_NO_BATCH");
         ctx->no_batch = nb && nb[0] == '1';
+        // pair lists above this many entries (8 B each) make a product run in row panels
+        ctx->pair_budget = (int64_t)1 << 30;
+        if (const char *pb = getenv("BSP_PAIR_BUDGET")) {
+            const long long v = atoll(pb);
+            if (v > 0) ctx->pair_budget = v;
+        }
     }
     // keep freed blocks in the stream-ordered pool: a chain allocates and frees every product
     cudaMemPool_t pool;
@@ -235,6 +262,10 @@ void bsp_ctx_destroy(bsp_ctx *ctx)
     for (int i = 0; i < 32; i++)
         if (ctx->trace_ev[i]) cudaEventDestroy(ctx->trace_ev[i]);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (int i = 0; i < 2; i++) {
+        if (ctx->io_buf[i]) cudaFreeHost(ctx->io_buf[i]);
+        if (ctx->io_ev[i]) cudaEventDestroy(ctx->io_ev[i]);
+    }
     if (ctx->d_counters) cudaFree(ctx->d_counters);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->owns_stream && ctx->stream) cudaStreamDestroy(ctx->stream);

@@ -26,9 +26,12 @@ struct bsp_ctx {
     cudaEvent_t ev[4];
     void *pinned;        // small pinned staging area for scalar read-backs
     size_t pinned_bytes;
+    char *io_buf[2];     // pinned staging pieces of the binary reader/writer, allocated on first use
+    cudaEvent_t io_ev[2];
     void *d_counters;    // 256 B of device counters (exact-refold count of the numeric pass)
     bool force_generic;  // BSP_FORCE_GENERIC=1: always use the any-k exact numeric kernel (tests)
     int f32_path;        // float32 products: 0 = auto (tensor cores for k = 32 / 64), 1 = SIMT, 2 = tensor cores
+    int64_t pair_budget; // tile products whose pair lists one symbolic pass may hold (BSP_PAIR_BUDGET); more -> row panels
     bool no_batch;       // BSP_NO_BATCH=1: a chain level is never run as one stacked product (tests, comparisons)
     bool trace;          // BSP_TRACE=1: per-sub-phase device timings of every product on stderr
     int ntrace;
@@ -156,6 +159,12 @@ struct bsp_symbolic_out {
                          //          ascending inner block index inside a tile
     int64_t nnzb_c;
     int64_t nprod;
+    // When the pair lists of the requested rows would exceed pair_budget entries and the range holds
+    // more than one non-empty row, nothing is filled: n_split > 0 and split[0..n_split] are row
+    // boundaries of panels whose pair lists fit (a single row above the budget gets a panel of its own).
+    int64_t pair_budget; // in: 0 = no limit
+    int32_t n_split;     // out
+    int32_t *split;      // out: malloc'ed [n_split+1], the caller frees
 };
 
 // GPU symbolic pass (replaces the host hash maps of cu:141-176 and the pack loop cu:189-218)

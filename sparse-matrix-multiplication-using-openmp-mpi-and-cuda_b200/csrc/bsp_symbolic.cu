@@ -20,6 +20,7 @@
 //   4*nnzb(A) + 4*nprod + 4*nnzb(C) + 12*(nbr+1), plus the pair lists this design adds:
 //   8*nprod + 8*(nnzb(C)+1).
 #include <cstdlib>
+#include <vector>
 
 #include "bsp_internal.h"
 
@@ -245,6 +246,7 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     //    its A entry by binary search in the offset table, read its block column from B once,
     //    keep it in shared memory (in the area the pairs will occupy later) and set its bit
     int *tmpc = (int *)sp;
+    int *scol = tmpc + pcap; // [T <= pcap] sorted block columns of the C row, staged for a coalesced store
     // every thread owns a contiguous run of products [x0, x1): one binary search for the A entry
     // of x0, then it walks forward (runs are ~P/512 long, so consecutive lanes read consecutive
     // memory and the run length being odd keeps the shared-memory stores conflict-free)
@@ -261,14 +263,30 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         e_run = lo;
     }
     {
+        // the loads of one batch are independent, so their L2 latencies overlap
+        constexpr int UB = 8;
         int e = e_run;
         int2 ae = aent[e];
         int next_off = aent[e + 1].y;
-        for (int x = x0; x < x1; x++) {
-            while (x >= next_off) { e++; ae = aent[e]; next_off = aent[e + 1].y; }
-            const int c = b_colidx[ae.x + (x - ae.y)];
-            tmpc[x] = c;
-            atomicOr(&bm[c >> 5], 1u << (c & 31));
+        for (int xb = x0; xb < x1; xb += UB) {
+            int addr[UB], cv[UB];
+#pragma unroll
+            for (int u = 0; u < UB; u++) {
+                const int x = xb + u;
+                addr[u] = -1;
+                if (x < x1) {
+                    while (x >= next_off) { e++; ae = aent[e]; next_off = aent[e + 1].y; }
+                    addr[u] = ae.x + (x - ae.y);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UB; u++) cv[u] = addr[u] >= 0 ? b_colidx[addr[u]] : 0;
+#pragma unroll
+            for (int u = 0; u < UB; u++)
+                if (addr[u] >= 0) {
+                    tmpc[xb + u] = cv[u];
+                    atomicOr(&bm[cv[u] >> 5], 1u << (cv[u] & 31));
+                }
         }
     }
     __syncthreads();
@@ -282,16 +300,17 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         if (w < words) {
             wrank[w] = (uint32_t)(carry + ex);
             uint32_t b = bits;
-            int o = cbase + carry + ex;
+            int o = carry + ex;
             while (b) {
                 const int bit = __ffs(b) - 1;
                 b &= b - 1;
-                c_colidx[o++] = w * 32 + bit;
+                scol[o++] = w * 32 + bit;
             }
         }
         carry += tot;
     }
     __syncthreads();
+    for (int t = tid; t < T; t += FILL_THREADS) c_colidx[cbase + t] = scol[t];
     // 3. output tile of every product (16-bit rank in the row) + pairs per tile
     for (int x = x0; x < x1; x++) {
         const int c = tmpc[x];
@@ -301,19 +320,18 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     }
     __syncthreads();
     // 4. exclusive scan -> first slot of every tile; publish pair_ptr; cur[] becomes the cursor
-    carry = 0;
+    //    (every thread scans a contiguous chunk of tiles serially; one block scan joins the chunks)
     int maxcnt = 0;
-    for (int t0 = 0; t0 < T; t0 += FILL_THREADS) {
-        const int t = t0 + tid;
-        const int v = t < T ? cur[t] : 0;
-        maxcnt = max(maxcnt, v);
+    {
+        const int ch = (T + FILL_THREADS - 1) / FILL_THREADS;
+        const int t0 = min(tid * ch, T), t1 = min(t0 + ch, T);
+        int sum = 0;
+        for (int t = t0; t < t1; t++) { const int v = cur[t]; sum += v; maxcnt = max(maxcnt, v); }
         int tot;
-        const int ex = block_excl_scan_i32(v, sm33, &tot);
-        if (t < T) {
-            cur[t] = carry + ex;
-            pair_ptr[(size_t)cbase + t] = pbase + carry + ex;
-        }
-        carry += tot;
+        int ex = block_excl_scan_i32(sum, sm33, &tot);
+        for (int t = t0; t < t1; t++) { const int v = cur[t]; cur[t] = ex; ex += v; }
+        __syncthreads();
+        for (int t = tid; t < T; t += FILL_THREADS) pair_ptr[(size_t)cbase + t] = pbase + cur[t];
     }
     maxcnt = __syncthreads_or(maxcnt > FILL_SORT_MAX);
     if (!maxcnt) {
@@ -339,6 +357,7 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
                 while (j >= s1 && sp[j].x > v.x) { sp[j + 1] = sp[j]; j--; }
                 sp[j + 1] = v;
             }
+            sp[e1 - 1].y |= (int)0x80000000; // 6. last pair of the tile
         }
         __syncthreads();
     } else {
@@ -360,8 +379,10 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     }
     // 6. mark the last pair of every tile (sign bit of .y): the numeric pass finds tile ends
     //    in the pair stream itself instead of chasing pair_ptr
-    for (int t = tid; t < T; t += FILL_THREADS) sp[cur[t] - 1].y |= (int)0x80000000;
-    __syncthreads();
+    if (maxcnt) {
+        for (int t = tid; t < T; t += FILL_THREADS) sp[cur[t] - 1].y |= (int)0x80000000;
+        __syncthreads();
+    }
     // 7. stream the row's pairs out
     for (int x = tid; x < P; x += FILL_THREADS) pairs[pbase + x] = sp[x];
 }
@@ -642,7 +663,9 @@ __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowp
 int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo, int32_t row_hi,
                  bsp_symbolic_out *out)
 {
+    const int64_t pair_budget = out->pair_budget; // the one input field
     memset(out, 0, sizeof(*out));
+    out->pair_budget = pair_budget;
     const int nbr = A->nbr;
     const int words = (B->nbc + 31) / 32 > 0 ? (B->nbc + 31) / 32 : 1;
     const size_t smem_count = (size_t)SYM_WARPS * words * sizeof(uint32_t);
@@ -730,6 +753,32 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     int ncls[NCLASS];
     for (int c = 0; c < NCLASS; c++) ncls[c] = h_counts[c];
     if (out->nnzb_c < 0) BSP_FAIL(ctx, BSP_ERR_LIMIT, "product has more than 2^31-1 tiles");
+    out->n_split = 0;
+    out->split = nullptr;
+    if (out->pair_budget > 0 && out->nprod > out->pair_budget) {
+        // too many tile products for one pair list: hand back row panels that fit (greedy over the
+        // per-row product counts, which are already on the device as a prefix sum)
+        std::vector<int64_t> pp((size_t)nbr + 1);
+        BSP_CUDA(ctx, cudaMemcpyAsync(pp.data(), row_prod_ptr, ((size_t)nbr + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+        BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        const int lo = row_lo < 0 ? 0 : row_lo, hi = row_hi > nbr ? nbr : row_hi;
+        std::vector<int32_t> cuts;
+        cuts.push_back(lo);
+        int start = lo;
+        for (int r = lo; r < hi; r++) {
+            if (pp[r + 1] - pp[start] > out->pair_budget && r > start) { cuts.push_back(r); start = r; }
+        }
+        cuts.push_back(hi);
+        if (cuts.size() > 2) {
+            out->n_split = (int32_t)cuts.size() - 1;
+            out->split = (int32_t *)malloc(cuts.size() * sizeof(int32_t));
+            if (!out->split) BSP_FAIL(ctx, BSP_ERR_NOMEM, "symbolic pass: panel list");
+            memcpy(out->split, cuts.data(), cuts.size() * sizeof(int32_t));
+            out->c_rowptr = nullptr; // released by the scratch guard
+            out->c_colidx = nullptr; out->pair_ptr = nullptr; out->pairs = nullptr;
+            return BSP_OK;
+        }
+    }
 
     BSP_TRY(sc.alloc(&out->c_colidx, (size_t)out->nnzb_c));
     BSP_TRY(sc.alloc(&out->pair_ptr, (size_t)out->nnzb_c + 1));

@@ -1,6 +1,6 @@
 // a4 -- drop-in for the reference's command line (cu:402-682):
 //
-//     a4 <folder> [--ranks P] [--devices D]
+//     a4 <folder> [--ranks P] [--devices D] [--binary] [--checksum] [--no-output]
 //
 // Reads <folder>/size ("N k": number of matrices and tile edge, cu:411-419) and
 // <folder>/matrix1..N, multiplies the chain M1*M2*...*MN and writes the product to ./matrix in
@@ -15,6 +15,12 @@
 // same tree (cu:569-571), and all-zero tiles are dropped from the final product (cu:577-592).
 // Sub-chain r runs on CUDA device r mod D on its own host thread; partial products move
 // device-to-device into device 0, which does the merge.  Default P = 1, D = all visible.
+//
+// Additions without a counterpart in the reference (off by default, the default run is the
+// reference's): --binary reads <folder>/matrixI.bin where it exists (else the text file) and
+// writes ./matrix.bin instead of ./matrix; --checksum prints "checksum <16 hex digits>" of the
+// final product (computed on the device); --no-output skips the output file (with --checksum:
+// compare a 20 GB product without writing it).
 //
 // Host code only: everything that touches the GPU goes through the C ABI of libbspgemm.so.
 #include <chrono>
@@ -39,18 +45,41 @@ struct Rank {
     std::string err;
 };
 
-void run_rank(Rank *r, const std::string &folder, int k)
+bool file_exists(const std::string &p)
+{
+    FILE *f = fopen(p.c_str(), "rb");
+    if (f) fclose(f);
+    return f != nullptr;
+}
+
+void run_rank(Rank *r, const std::string &folder, int k, bool binary)
 {
     r->rc = bsp_ctx_create(r->device, nullptr, &r->ctx);
     if (r->rc) { r->err = r->ctx ? bsp_last_error(r->ctx) : "context"; return; }
     const int n = r->end - r->start + 1;
     r->mats.assign((size_t)n, nullptr);
-    // (the reference parses its files with one OpenMP task each, cu:334-339; here the
-    // sub-chains already run on one host thread per rank and a context is not thread-safe)
+    // The reference parses its files with one OpenMP task each (cu:334-339).  Here the text files of
+    // the sub-chain go through the pipelined reader: host threads parse into pinned buffers while this
+    // thread uploads and builds the finished ones.
+    std::vector<std::string> text_paths;
+    std::vector<size_t> text_slot;
     for (int i = 0; i < n && !r->rc; i++) {
-        std::string path = folder + "/matrix" + std::to_string(r->start + i + 1); // 1-based, cu:338-344
-        r->rc = bsp_mat_read_text(r->ctx, path.c_str(), k, &r->mats[(size_t)i]);
+        const std::string path = folder + "/matrix" + std::to_string(r->start + i + 1); // 1-based, cu:338-344
+        if (binary && file_exists(path + ".bin")) {
+            r->rc = bsp_mat_read_bin(r->ctx, (path + ".bin").c_str(), &r->mats[(size_t)i]);
+            if (r->rc) r->err = bsp_last_error(r->ctx);
+        } else {
+            text_paths.push_back(path);
+            text_slot.push_back((size_t)i);
+        }
+    }
+    if (!r->rc && !text_paths.empty()) {
+        std::vector<const char *> cp;
+        for (auto &p : text_paths) cp.push_back(p.c_str());
+        std::vector<bsp_mat *> got(cp.size(), nullptr);
+        r->rc = bsp_mat_read_text_many(r->ctx, cp.data(), (int32_t)cp.size(), k, got.data());
         if (r->rc) r->err = bsp_last_error(r->ctx);
+        else for (size_t j = 0; j < got.size(); j++) r->mats[text_slot[j]] = got[j];
     }
     if (r->rc) return;
     std::vector<char> log((size_t)n * 64 + 64);
@@ -65,15 +94,20 @@ int main(int argc, char **argv)
 {
     auto t0 = std::chrono::high_resolution_clock::now();
     if (argc < 2) {
-        fprintf(stderr, "usage: %s <folder> [--ranks P] [--devices D]\n", argv[0]);
+        fprintf(stderr, "usage: %s <folder> [--ranks P] [--devices D] [--binary] [--checksum] [--no-output]\n", argv[0]);
         return 2;
     }
     std::string folder = argv[1];
     int P = getenv("BSP_RANKS") ? atoi(getenv("BSP_RANKS")) : 1;
     int D = 0;
-    for (int i = 2; i + 1 < argc; i += 2) {
-        if (!strcmp(argv[i], "--ranks") || !strcmp(argv[i], "--gpus")) P = atoi(argv[i + 1]);
-        else if (!strcmp(argv[i], "--devices")) D = atoi(argv[i + 1]);
+    bool binary = false, want_checksum = false, no_output = false;
+    for (int i = 2; i < argc; i++) {
+        if ((!strcmp(argv[i], "--ranks") || !strcmp(argv[i], "--gpus")) && i + 1 < argc) P = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--devices") && i + 1 < argc) D = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--binary")) binary = true;
+        else if (!strcmp(argv[i], "--checksum")) want_checksum = true;
+        else if (!strcmp(argv[i], "--no-output")) no_output = true;
+        else { fprintf(stderr, "a4: unknown argument %s\n", argv[i]); return 2; }
     }
     if (P < 1) P = 1;
 
@@ -122,7 +156,7 @@ int main(int argc, char **argv)
     for (size_t r = 0; r < ranks.size(); r++) ranks[r].device = (int)(r % (size_t)D);
     {
         std::vector<std::thread> th;
-        for (auto &r : ranks) th.emplace_back(run_rank, &r, folder, k);
+        for (auto &r : ranks) th.emplace_back(run_rank, &r, folder, k, binary);
         for (auto &t : th) t.join();
     }
     int rc = 0;
@@ -161,7 +195,14 @@ int main(int argc, char **argv)
         }
     }
     if (!rc) {
-        if (bsp_prune_zero(probe, result) || bsp_mat_write_text(probe, result, "matrix")) {
+        int e = bsp_prune_zero(probe, result);
+        if (!e && want_checksum) {
+            uint64_t sum = 0;
+            e = bsp_mat_checksum(probe, result, &sum);
+            if (!e) printf("checksum %016llx\n", (unsigned long long)sum);
+        }
+        if (!e && !no_output) e = binary ? bsp_mat_write_bin(probe, result, "matrix.bin") : bsp_mat_write_text(probe, result, "matrix");
+        if (e) {
             fprintf(stderr, "a4: output: %s\n", bsp_last_error(probe));
             rc = 3;
         }

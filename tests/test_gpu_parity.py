@@ -398,3 +398,40 @@ def test_multiply_host_pipelined_download(ctx):
     rbr, rbc, rv = ref.coo()
     assert st.nprod == nprod and st.nnzb_c == ref.nnzb
     assert np.array_equal(br, rbr) and np.array_equal(bc, rbc) and np.array_equal(v, rv)
+
+
+def test_products_above_the_pair_budget_run_in_row_panels(monkeypatch):
+    """A product whose pair lists (8 B per tile product) exceed the context's budget -- dense x
+    dense chain levels hold G^3 of them -- is computed in row panels and concatenated; bit-exact
+    against the oracle and the unsplit run, same statistics.  BSP_PAIR_BUDGET makes the split
+    happen at test sizes; a single row above the budget still gets a panel of its own."""
+    k, G = 4, 48
+    dense = [bsp_gen.random_matrix(G * k, G * k, k, 1.0, 60 + i, "edgy" if i else "u64") for i in range(2)]
+    sparse = [bsp_gen.random_matrix(300 * k, 300 * k, k, 0.05, 70 + i, "u64") for i in range(2)]
+    hub = list(bsp_gen.random_matrix(200 * k, 200 * k, k, 0.02, 80, "u64"))
+    # block row 7 becomes full (duplicates: the last one wins): one row far above the budget
+    hub[3] = np.concatenate([hub[3], np.full(200, 7, np.int32)])
+    hub[4] = np.concatenate([hub[4], np.arange(200, dtype=np.int32)])
+    hub[5] = np.concatenate([hub[5].reshape(-1, k, k), bsp_gen.values(81, 200 * k * k, "u64").reshape(-1, k, k)])
+    cases = [(dense[0], dense[1]), (sparse[0], sparse[1]), (tuple(hub), tuple(hub))]
+    plain = bspgemm.Context(0)
+    monkeypatch.setenv("BSP_PAIR_BUDGET", "3000")
+    split = bspgemm.Context(0)
+    monkeypatch.delenv("BSP_PAIR_BUDGET")
+    try:
+        for a, b in cases:
+            want, nprod = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))
+            s1, s2 = bspgemm.Stats(), bspgemm.Stats()
+            c1 = plain.helper(plain.matrix_from_coo(*a), plain.matrix_from_coo(*b), stats=s1)
+            c2 = split.helper(split.matrix_from_coo(*a), split.matrix_from_coo(*b), stats=s2)
+            assert_same(c1, want)
+            assert_same(c2, want)
+            assert s1.nprod == s2.nprod == nprod and s1.nnzb_c == s2.nnzb_c == want.nnzb
+            assert s2.launches > s1.launches        # it really ran as several panels
+            assert c1.checksum() == c2.checksum()
+        # a chain through the split context (levels of a densifying chain) equals the oracle's tree
+        mats = [bsp_gen.random_matrix(40 * k, 40 * k, k, 0.15, 90 + i, "u64") for i in range(6)]
+        want, _ = orc.chain([orc.OMat.from_coo(*m) for m in mats])
+        assert_same(split.helper2([split.matrix_from_coo(*m) for m in mats]), want)
+    finally:
+        plain.close(); split.close()
