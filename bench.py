@@ -241,7 +241,9 @@ def run_chain(torch, dist, ctx, rank, world, steps, warmup):
     def one():
         nonlocal nprod, sent
         st = bspgemm.Stats()
+        tr = bsp_dist._phase_tracer(rank)
         partial = ctx.helper2(mats, stats=st) if mats else None
+        tr("local sub-chain")
         nprod = st.nprod
         if world == 1:
             return partial

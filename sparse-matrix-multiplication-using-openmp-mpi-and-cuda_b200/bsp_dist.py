@@ -184,6 +184,25 @@ def merge_groups(nparts):
     return out
 
 
+def _phase_tracer(rank):
+    """BSP_DIST_TRACE=1: rank 0 prints the wall-clock time of every phase of the merge (with a device
+    synchronisation before each reading, so the numbers add up but the run is slower)."""
+    import os
+    import sys
+    import time
+    if os.environ.get("BSP_DIST_TRACE") != "1" or rank != 0:
+        return lambda label: None
+    import torch
+    last = [time.perf_counter()]
+
+    def mark(label):
+        torch.cuda.synchronize()
+        now = time.perf_counter()
+        sys.stderr.write("[bsp dist] %-22s %8.3f ms\n" % (label, (now - last[0]) * 1e3))
+        last[0] = now
+    return mark
+
+
 def tree_merge_panels(rank, nparts, partial, send, recv, send_rows, bcast, row_weights, multiply, concat):
     """Step-doubling merge in which every product is ROW-PANEL SHARDED over the ranks of its
     subtree instead of being computed by the receiving rank alone (the reference's rank 0
@@ -202,29 +221,37 @@ def tree_merge_panels(rank, nparts, partial, send, recv, send_rows, bcast, row_w
       concat(list_of_panels)                       one matrix
     Returns the final product on rank 0, None elsewhere."""
     held = partial
+    trace = _phase_tracer(rank)
     for s, group in merge_groups(nparts):
         if rank not in group:
             continue
         g = group[0]
+        trace("level s=%d start" % s)
         # 1. left: block-row panels from g;  right: from g+s to everybody in the group
         if rank == g:
             bounds = balanced_panels(row_weights(held), len(group))
+            trace("row weights")
             for i, r in enumerate(group):
                 if r != g:
                     send_rows(held, bounds[i], bounds[i + 1], r)
             left_rows = (held, bounds[0], bounds[1])
         else:
             left_rows = (recv(g), None, None)
+        trace("left panels moved")
         right = bcast(held if rank == g + s else None, g + s, group)
+        trace("right broadcast")
         # 2. this rank's panel
         if rank == g:
             panel = multiply(left_rows[0], right, (left_rows[1], left_rows[2]))
         else:
             panel = multiply(left_rows[0], right, None)
+        trace("panel product")
         # 3. gather on g
         if rank == g:
             panels = [panel] + [recv(r) for r in group[1:]]
+            trace("panels gathered")
             held = concat(panels)
+            trace("concat")
         else:
             send(panel, g)
             held = None

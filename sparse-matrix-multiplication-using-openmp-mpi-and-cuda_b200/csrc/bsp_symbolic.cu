@@ -550,6 +550,207 @@ sym_fill_global_kernel(const int32_t *__restrict__ rowlist, const int32_t *__res
     }
 }
 
+// ---- fill, very long rows: several CTAs per row, one phase per launch --------------------------------
+// sym_fill_global_kernel gives a row that does not fit in shared memory ONE CTA, which handles 0.3-0.4
+// tile products per ns: fine for 10^4..10^5 products per row (all rows run side by side), but an R-MAT
+// hub row or a dense chain level (10^6..10^7 products in one row) becomes the tail of the whole pass.
+// Such rows (more than hv_min products) take this path instead: the same steps as separate launches,
+// those that touch every product spread over the whole GPU, one warp per (row, A entry):
+//   hv_pattern   one CTA per row: column bitmap -> rank table (both kept in global memory), colidx of C
+//   hv_products<false>  counts per output tile (global atomics)
+//   hv_scan      one CTA per row: counts -> first slot of every tile (pair_ptr and the cursor array)
+//   hv_products<true>   every product takes the next free slot of its tile (atomic cursor): any order
+//   hv_sort_small / hv_sort_big   each tile's pairs sorted by A index, which is ascending inner block
+//                index j because the A row is sorted -- the order the arithmetic needs; the last pair
+//                of a tile gets its end flag here
+// It moves every pair twice (scattered 8-byte stores, then the sort), about 2x the one-CTA kernel's
+// total cost, so it is used only where that kernel's latency, not its throughput, is the problem.
+constexpr int HV_THREADS = 256;
+constexpr int HV_SORT_CAP = 8192; // pairs of one tile sorted in shared memory (64 KB); longer lists are sorted in place
+
+__global__ void __launch_bounds__(HV_THREADS)
+hv_pattern_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
+                  const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
+                  const int32_t *__restrict__ b_colidx, int words, const int32_t *__restrict__ c_rowptr,
+                  int32_t *__restrict__ c_colidx, uint32_t *__restrict__ gbm, uint32_t *__restrict__ grank,
+                  int32_t *__restrict__ ent_cnt)
+{
+    extern __shared__ uint32_t bm[];
+    __shared__ int sm33[33];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = HV_THREADS / 32;
+    const int h = blockIdx.x, row = rowlist[h];
+    for (int w = tid; w < words; w += HV_THREADS) bm[w] = 0u;
+    __syncthreads();
+    const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
+    for (int p = a0 + warp; p < a1; p += nwarp) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            atomicOr(&bm[c >> 5], 1u << (c & 31));
+        }
+    }
+    __syncthreads();
+    const int cbase = c_rowptr[row];
+    int carry = 0;
+    for (int w0 = 0; w0 < words; w0 += HV_THREADS) {
+        const int w = w0 + tid;
+        const uint32_t bits = w < words ? bm[w] : 0u;
+        int tot;
+        const int ex = block_excl_scan_i32(__popc(bits), sm33, &tot);
+        if (w < words) {
+            gbm[(size_t)h * words + w] = bits;
+            grank[(size_t)h * words + w] = (uint32_t)(carry + ex);
+            uint32_t b = bits;
+            int o = cbase + carry + ex;
+            while (b) {
+                const int bit = __ffs(b) - 1;
+                b &= b - 1;
+                c_colidx[o++] = w * 32 + bit;
+            }
+        }
+        carry += tot;
+    }
+    if (tid == 0) ent_cnt[h] = a1 - a0;
+}
+
+// one warp per (heavy row, A entry), lanes over the tiles of B row j
+template <bool PLACE>
+__global__ void __launch_bounds__(HV_THREADS)
+hv_products_kernel(const int32_t *__restrict__ rowlist, int nheavy, const int32_t *__restrict__ ent_ptr,
+                   const int32_t *__restrict__ a_rowptr, const int32_t *__restrict__ a_colidx, int b_nbr,
+                   const int32_t *__restrict__ b_rowptr, const int32_t *__restrict__ b_colidx, int words,
+                   const uint32_t *__restrict__ gbm, const uint32_t *__restrict__ grank,
+                   const int32_t *__restrict__ c_rowptr, unsigned long long *__restrict__ cur, int2 *__restrict__ pairs)
+{
+    const int lane = threadIdx.x & 31;
+    const int gw = (blockIdx.x * HV_THREADS + threadIdx.x) >> 5, nw = (gridDim.x * HV_THREADS) >> 5;
+    const int total = ent_ptr[nheavy];
+    for (int item = gw; item < total; item += nw) {
+        int lo = 0, hi = nheavy; // heavy row of the item: last h with ent_ptr[h] <= item
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (ent_ptr[mid] <= item) lo = mid; else hi = mid;
+        }
+        const int row = rowlist[lo];
+        const int p = a_rowptr[row] + (item - ent_ptr[lo]);
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        const size_t cbase = (size_t)c_rowptr[row];
+        const uint32_t *bmh = gbm + (size_t)lo * words, *rkh = grank + (size_t)lo * words;
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            const int t = (int)rkh[c >> 5] + __popc(bmh[c >> 5] & ((1u << (c & 31)) - 1u));
+            const unsigned long long pos = atomicAdd(&cur[cbase + t], 1ull);
+            if (PLACE) pairs[pos] = make_int2(p, q);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(HV_THREADS)
+hv_scan_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ c_rowptr,
+               const int64_t *__restrict__ row_prod_ptr, unsigned long long *__restrict__ cur,
+               int64_t *__restrict__ pair_ptr)
+{
+    __shared__ int sm33[33];
+    const int tid = threadIdx.x;
+    const int row = rowlist[blockIdx.x];
+    const int cbase = c_rowptr[row], T = c_rowptr[row + 1] - cbase;
+    const int64_t pbase = row_prod_ptr[row];
+    int carry = 0;
+    for (int t0 = 0; t0 < T; t0 += HV_THREADS) {
+        const int t = t0 + tid;
+        const int v = t < T ? (int)cur[(size_t)cbase + t] : 0;
+        int tot;
+        const int ex = block_excl_scan_i32(v, sm33, &tot);
+        if (t < T) {
+            const int64_t start = pbase + carry + ex;
+            pair_ptr[(size_t)cbase + t] = start;
+            cur[(size_t)cbase + t] = (unsigned long long)start;
+        }
+        carry += tot;
+    }
+}
+
+// tiles with at most 32 pairs: one warp per tile, bitonic network in registers; longer ones are listed
+__global__ void __launch_bounds__(HV_THREADS)
+hv_sort_small_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ c_rowptr,
+                     const int64_t *__restrict__ pair_ptr, const unsigned long long *__restrict__ cur,
+                     int2 *__restrict__ pairs, int32_t *__restrict__ big_list, int32_t *__restrict__ big_count)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = HV_THREADS / 32;
+    const int row = rowlist[blockIdx.x];
+    const int cbase = c_rowptr[row], T = c_rowptr[row + 1] - cbase;
+    for (int t = blockIdx.y * nwarp + warp; t < T; t += gridDim.y * nwarp) {
+        const int64_t s0 = pair_ptr[(size_t)cbase + t];
+        const int L = (int)((int64_t)cur[(size_t)cbase + t] - s0);
+        if (L > 32) {
+            if (lane == 0) big_list[atomicAdd(big_count, 1)] = cbase + t;
+            continue;
+        }
+        int2 v = make_int2(0x7fffffff, 0);
+        if (lane < L) v = pairs[s0 + lane];
+        if (L > 1) {
+#pragma unroll
+            for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+                for (int stride = size >> 1; stride > 0; stride >>= 1) {
+                    const int ox = __shfl_xor_sync(0xffffffffu, v.x, stride);
+                    const int oy = __shfl_xor_sync(0xffffffffu, v.y, stride);
+                    const bool up = (lane & size) == 0;          // ascending block
+                    const bool lower = (lane & stride) == 0;     // this lane keeps the smaller of the two
+                    const bool take = (lower == up) ? (ox < v.x) : (ox > v.x);
+                    if (take) { v.x = ox; v.y = oy; }
+                }
+            }
+        }
+        if (lane == L - 1) v.y |= (int)0x80000000;
+        if (lane < L) pairs[s0 + lane] = v;
+    }
+}
+
+// longer lists: one CTA per tile, bitonic sort in shared memory, or in a per-CTA global scratch area of
+// `scratch_stride` pairs when a list exceeds HV_SORT_CAP (a tile with more than 8192 pairs needs an A
+// row with more than 8192 entries; the host sizes the scratch from the column count of A)
+__global__ void __launch_bounds__(HV_THREADS)
+hv_sort_big_kernel(const int32_t *__restrict__ big_list, const int32_t *__restrict__ big_count,
+                   const int64_t *__restrict__ pair_ptr, const unsigned long long *__restrict__ cur,
+                   int2 *pairs, int2 *scratch, size_t scratch_stride)
+{
+    extern __shared__ __align__(16) uint32_t hv_smem[];
+    const int tid = threadIdx.x;
+    const int n = *big_count;
+    for (int i = blockIdx.x; i < n; i += gridDim.x) {
+        const int tile = big_list[i];
+        const int64_t s0 = pair_ptr[tile];
+        const int L = (int)((int64_t)cur[tile] - s0);
+        int N = 64;
+        while (N < L) N <<= 1;
+        int2 *a = N <= HV_SORT_CAP ? (int2 *)hv_smem : scratch + (size_t)blockIdx.x * scratch_stride;
+        for (int x = tid; x < N; x += HV_THREADS) a[x] = x < L ? pairs[s0 + x] : make_int2(0x7fffffff, 0);
+        __syncthreads();
+        for (int size = 2; size <= N; size <<= 1) {
+            for (int stride = size >> 1; stride > 0; stride >>= 1) {
+                for (int x = tid; x < N / 2; x += HV_THREADS) {
+                    const int lo = ((x / stride) * stride * 2) + (x % stride), hi = lo + stride;
+                    const bool up = (lo & size) == 0;
+                    const int2 u = a[lo], w = a[hi];
+                    if ((u.x > w.x) == up) { a[lo] = w; a[hi] = u; }
+                }
+                __syncthreads();
+            }
+        }
+        for (int x = tid; x < L; x += HV_THREADS) {
+            int2 v = a[x];
+            if (x == L - 1) v.y |= (int)0x80000000;
+            pairs[s0 + x] = v;
+        }
+        __syncthreads();
+    }
+}
+
 // ---- fill, tiny rows: one WARP per block row, no bitmap ------------------------------------------
 // A row with at most TINY_P tile products and TINY_A entries in its A row is sorted instead of
 // bit-mapped: every product gets the key (block column << 5 | ordinal of its A entry); a bitonic
@@ -640,12 +841,13 @@ sym_fill_tiny_kernel(const int32_t *__restrict__ rowlist, int nrows, const int32
 // ---- rows -> capacity classes -----------------------------------------------------------------
 // class c rows go to lists[c * nbr ...]; counts[c] = rows in class c.  A row with P tile
 // products fits class c when P <= caps[c]; larger than every cap -> class NCLASS-1 (global).
-constexpr int NCLASS = 5; // 0: tiny rows (warp + sort), 1..3: shared-memory CTA classes, 4: global-memory CTA
+constexpr int NCLASS = 6; // 0: tiny rows (warp + sort), 1..3: shared-memory CTA classes, 4: global-memory CTA,
+                          // 5: rows so long that one CTA would be the tail of the pass -> multi-launch path
 
 __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowptr,
                                      const int32_t *__restrict__ row_cnt, const int32_t *__restrict__ row_prod,
                                      int cap0, int cap1, int cap2, int tcap0, int tcap1, int tcap2, int acap,
-                                     int tiny_ok, int32_t *__restrict__ lists, int32_t *__restrict__ counts)
+                                     int tiny_ok, int hv_min, int32_t *__restrict__ lists, int32_t *__restrict__ counts)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nbr || row_cnt[row] == 0) return;
@@ -654,8 +856,74 @@ __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowp
     int cls = (P <= cap0 && T <= tcap0) ? 1 : ((P <= cap1 && T <= tcap1) ? 2 : ((P <= cap2 && T <= tcap2) ? 3 : 4));
     if (nA > acap) cls = 4;                                  // A row too long for the shared-memory entry table
     if (tiny_ok && P <= TINY_P && nA <= TINY_A) cls = 0;     // warp-per-row sort
+    if (cls == 4 && P > hv_min) cls = 5;                     // spread over the whole GPU
     const int slot = atomicAdd(&counts[cls], 1);
     lists[(size_t)cls * nbr + slot] = row;
+}
+
+// multi-launch fill of the rows that do not fit the shared-memory classes (see "heavy rows" above)
+int fill_heavy_rows(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const int32_t *rowlist, int nheavy, int words,
+                    const bsp_symbolic_out *out, const int64_t *row_prod_ptr)
+{
+    bsp_scratch sc(ctx);
+    unsigned long long *cur = nullptr;
+    uint32_t *gbm = nullptr, *grank = nullptr;
+    int32_t *ent_cnt = nullptr, *ent_ptr = nullptr, *big_list = nullptr, *big_count = nullptr;
+    int2 *scratch = nullptr;
+    // heavy rows are processed in batches so that their bitmaps and rank tables stay below 256 MB
+    int hb = (int)(((size_t)256 << 20) / ((size_t)words * 8));
+    if (hb < 1) hb = 1;
+    if (hb > nheavy) hb = nheavy;
+    int64_t big_cap = out->nprod / 33 + 1;
+    if (big_cap > out->nnzb_c) big_cap = out->nnzb_c;
+    BSP_TRY(sc.alloc(&cur, (size_t)out->nnzb_c + 1));
+    BSP_TRY(sc.alloc(&gbm, (size_t)hb * words));
+    BSP_TRY(sc.alloc(&grank, (size_t)hb * words));
+    BSP_TRY(sc.alloc(&ent_cnt, (size_t)hb + 1));
+    BSP_TRY(sc.alloc(&ent_ptr, (size_t)hb + 1));
+    BSP_TRY(sc.alloc(&big_list, (size_t)big_cap));
+    BSP_TRY(sc.alloc(&big_count, 1));
+    const int grid_big = ctx->sm_count * 2;
+    size_t scratch_stride = 0;
+    {
+        size_t n = 64;
+        while (n < (size_t)A->nbc) n <<= 1; // a tile cannot have more pairs than the A row has entries
+        if (n > (size_t)HV_SORT_CAP) {
+            scratch_stride = n;
+            BSP_TRY(sc.alloc(&scratch, scratch_stride * grid_big));
+        }
+    }
+    BSP_CUDA(ctx, cudaMemsetAsync(cur, 0, ((size_t)out->nnzb_c + 1) * sizeof(unsigned long long), ctx->stream));
+    BSP_CUDA(ctx, cudaFuncSetAttribute(hv_sort_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HV_SORT_CAP * 8));
+    const int grid = ctx->sm_count * 8;
+    for (int h0 = 0; h0 < nheavy; h0 += hb) {
+        const int n = nheavy - h0 < hb ? nheavy - h0 : hb;
+        const int32_t *rl = rowlist + h0;
+        BSP_CUDA(ctx, cudaMemsetAsync(ent_cnt + n, 0, sizeof(int32_t), ctx->stream));
+        BSP_CUDA(ctx, cudaMemsetAsync(big_count, 0, sizeof(int32_t), ctx->stream));
+        hv_pattern_kernel<<<n, HV_THREADS, (size_t)words * sizeof(uint32_t), ctx->stream>>>(
+            rl, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, out->c_rowptr, out->c_colidx, gbm, grank, ent_cnt);
+        BSP_LAUNCH_CHECK(ctx);
+        BSP_TRY(bsp_scan_i32(ctx, ent_cnt, ent_ptr, (int64_t)n + 1, nullptr));
+        hv_products_kernel<false><<<grid, HV_THREADS, 0, ctx->stream>>>(rl, n, ent_ptr, A->rowptr, A->colidx, B->nbr, B->rowptr,
+                                                                       B->colidx, words, gbm, grank, out->c_rowptr, cur, out->pairs);
+        BSP_LAUNCH_CHECK(ctx);
+        hv_scan_kernel<<<n, HV_THREADS, 0, ctx->stream>>>(rl, out->c_rowptr, row_prod_ptr, cur, out->pair_ptr);
+        BSP_LAUNCH_CHECK(ctx);
+        hv_products_kernel<true><<<grid, HV_THREADS, 0, ctx->stream>>>(rl, n, ent_ptr, A->rowptr, A->colidx, B->nbr, B->rowptr,
+                                                                      B->colidx, words, gbm, grank, out->c_rowptr, cur, out->pairs);
+        BSP_LAUNCH_CHECK(ctx);
+        int y = ctx->sm_count * 16 / n;
+        if (y < 1) y = 1;
+        if (y > 64) y = 64;
+        hv_sort_small_kernel<<<dim3((unsigned)n, (unsigned)y), HV_THREADS, 0, ctx->stream>>>(rl, out->c_rowptr, out->pair_ptr, cur,
+                                                                                            out->pairs, big_list, big_count);
+        BSP_LAUNCH_CHECK(ctx);
+        hv_sort_big_kernel<<<grid_big, HV_THREADS, HV_SORT_CAP * 8, ctx->stream>>>(big_list, big_count, out->pair_ptr, cur,
+                                                                                  out->pairs, scratch, scratch_stride);
+        BSP_LAUNCH_CHECK(ctx);
+    }
+    return BSP_OK;
 }
 
 } // namespace
@@ -704,6 +972,11 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
             caps[0] = tcaps[0] = a; caps[1] = tcaps[1] = b; caps[2] = tcaps[2] = c;
         }
     }
+    // A row above hv_min tile products is not given to one CTA (0.3-0.4 products/ns: 1 ms per 3*10^5) but to the
+    // multi-launch path, whose cost is spread over the GPU; below it the one-CTA kernel is cheaper in total
+    // (measured: chain top product, 66 k products per row: 3.3 ms against 38 ms).  BSP_HV_MIN_P is a test hook.
+    int hv_min = 1 << 18;
+    if (const char *e = getenv("BSP_HV_MIN_P")) { const int v = atoi(e); if (v > 0) hv_min = v; }
     // the tiny-row kernel packs the block column into 27 bits; BSP_SYM_CAPS (a test hook) also switches it off
     const int tiny_ok = (B->nbc < (1 << 27) && !getenv("BSP_SYM_CAPS")) ? 1 : 0;
     for (int c = 0; c < 3; c++) {
@@ -732,7 +1005,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         }
         classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, A->rowptr, row_cnt, row_prod, caps[0],
                                                                         caps[1], caps[2], tcaps[0], tcaps[1], tcaps[2],
-                                                                        acap, tiny_ok, lists, counts);
+                                                                        acap, tiny_ok, hv_min, lists, counts);
         BSP_LAUNCH_CHECK(ctx);
     }
     bsp_trace_mark(ctx, "sym_count");
@@ -812,6 +1085,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
             row_prod_ptr, out->c_colidx, (unsigned long long *)out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
+    if (ncls[5] > 0) BSP_TRY(fill_heavy_rows(ctx, A, B, lists + (size_t)5 * nbr, ncls[5], words, out, row_prod_ptr));
     bsp_trace_mark(ctx, "sym_fill");
     sc.keep(out->c_rowptr); sc.keep(out->c_colidx); sc.keep(out->pair_ptr); sc.keep(out->pairs); // now the caller's
     return BSP_OK;

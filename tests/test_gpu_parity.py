@@ -435,3 +435,35 @@ def test_products_above_the_pair_budget_run_in_row_panels(monkeypatch):
         assert_same(split.helper2([split.matrix_from_coo(*m) for m in mats]), want)
     finally:
         plain.close(); split.close()
+
+
+def test_very_long_rows_multi_launch_fill(ctx, monkeypatch):
+    """Rows above hv_min tile products (BSP_HV_MIN_P lowers it to test sizes) go through the
+    multi-launch path: global bitmaps, atomic counts and cursors, then a sort of every tile's pairs
+    by inner index.  Covers tile lists of 1..32 pairs (warp sort), hundreds (shared-memory sort) and
+    > 8192 (global scratch sort); 'edgy' values make any pair out of order visible (the fold is order
+    dependent).  The one-CTA kernel (default at these sizes) must give the same bits."""
+    k, G = 4, 600
+    rows, cols, _, br, bc, v = bsp_gen.random_matrix(G * k, G * k, k, 0.01, 500, "edgy")
+    hub_r = np.repeat(np.array([3, 77, 599], np.int32), G)
+    hub_c = np.tile(np.arange(G, dtype=np.int32), 3)
+    a = (rows, cols, k, np.concatenate([br, hub_r]), np.concatenate([bc, hub_c]),
+         np.concatenate([v.reshape(-1, k, k), bsp_gen.values(501, 3 * G * k * k, "edgy").reshape(-1, k, k)]))
+    b = bsp_gen.random_matrix(G * k, G * k, k, 0.3, 502, "edgy")
+    want, _ = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b), threads=8)
+    s0, s1 = bspgemm.Stats(), bspgemm.Stats()
+    one_cta = ctx.helper(dev(ctx, a), dev(ctx, b), stats=s0)
+    assert_same(one_cta, want)
+    # one output tile with 9000 pairs: a full row of A (k = 1) times two full columns of B
+    n = 9000
+    a1 = (1, n, 1, np.zeros(n, np.int32), np.arange(n, dtype=np.int32), bsp_gen.values(510, n, "edgy"))
+    b1 = (n, 2, 1, np.repeat(np.arange(n, dtype=np.int32), 2), np.tile(np.array([0, 1], np.int32), n),
+          bsp_gen.values(511, 2 * n, "edgy"))
+    want1, nprod = orc.multiply(orc.OMat.from_coo(*a1), orc.OMat.from_coo(*b1))
+    assert nprod == 2 * n
+    assert_same(ctx.helper(dev(ctx, a1), dev(ctx, b1)), want1)
+    monkeypatch.setenv("BSP_HV_MIN_P", "10000")
+    multi = ctx.helper(dev(ctx, a), dev(ctx, b), stats=s1)
+    assert_same(multi, want)
+    assert s1.launches > s0.launches                 # the three hub rows (108 000 products each) took the other path
+    assert_same(ctx.helper(dev(ctx, a1), dev(ctx, b1)), want1)
