@@ -231,6 +231,7 @@ def run_chain(torch, dist, ctx, rank, world, steps, warmup):
     nprod = 0
     sent = 0
     gb = bsp_dist.GroupBroadcaster(dist, torch, len(parts), "cuda") if world > 1 else None
+    tp = bsp_dist.GpuTransport(torch, dist, ctx, len(parts)) if world > 1 else None
 
     def sync():
         torch.cuda.synchronize()
@@ -283,10 +284,17 @@ def run_chain(torch, dist, ctx, rank, world, steps, warmup):
             if pl is not None:
                 sent += pl.nbytes
             return bsp_dist.payload_to_matrix(torch, ctx, gb.bcast(pl, src, grp))
-        if os.environ.get("BSP_CHAIN_MERGE", "panels") == "rank0":  # the reference's shape: receiver multiplies alone
+        mode = os.environ.get("BSP_CHAIN_MERGE", "distributed")
+        if mode == "rank0":  # the reference's shape: the receiver multiplies alone
             return bsp_dist.tree_merge(rank, len(parts), partial, mul, send, recv)
-        return bsp_dist.tree_merge_panels(rank, len(parts), partial, send, recv, send_rows, bcast,
-                                          lambda m: bsp_dist.device_row_weights(torch, m), mul_panel, ctx.concat_panels)
+        if mode == "panels":  # sharded products, gathered on the group leader after every level
+            return bsp_dist.tree_merge_panels(rank, len(parts), partial, send, recv, send_rows, bcast,
+                                              lambda m: bsp_dist.device_row_weights(torch, m), mul_panel, ctx.concat_panels)
+        tp.sent = 0
+        out = bsp_dist.tree_merge_distributed(rank, len(parts), partial, tp.send, tp.recv, tp.send_rows, tp.bcast,
+                                              tp.row_weights, mul_panel, ctx.concat_panels, gather=tp.gather)
+        sent = tp.sent
+        return out
 
     res = None
     for _ in range(warmup):
@@ -309,7 +317,7 @@ def run_chain(torch, dist, ctx, rank, world, steps, warmup):
     k = CHAIN["k"]
     return {"ms": t.item(), "unit": "ms", "n_gpus": world, "scaling": "strong",
             "workload": "chain of %d matrices, n=%d, k=%d, banded pattern (half-band %d blocks, %.0f%% filled), uint64; "
-                        "sub-chains of %d per GPU, NCCL tree merge with row-panel sharded products" % (CHAIN["n_mats"], CHAIN["n"], k, CHAIN["half_band"],
+                        "sub-chains of %d per GPU, NCCL tree merge, every product row-panel sharded over its subtree, panels stay distributed" % (CHAIN["n_mats"], CHAIN["n"], k, CHAIN["half_band"],
                                                                       CHAIN["density"] * 100, CHAIN["n_mats"] // max(len(parts), 1)),
             "products": CHAIN["n_mats"] - 1, "nprod_total": int(w.item()), "result_nnzb": int(res.nnzb),
             "useful_gflops": 2.0 * k ** 3 * w.item() / (t.item() * 1e-3) / 1e9,

@@ -258,6 +258,87 @@ def tree_merge_panels(rank, nparts, partial, send, recv, send_rows, bcast, row_w
     return held if rank == 0 else None
 
 
+def panel_orders(nparts):
+    """For tree_merge_distributed: which ranks hold the block-row panels of every intermediate
+    product, in ascending row order.  Returns (levels, final): levels[i] = (s, group, left_order,
+    right_order) for merge_groups(nparts)[i], final = order of the last product's panels."""
+    order = {r: [r] for r in range(nparts)}
+    levels = []
+    for s, group in merge_groups(nparts):
+        g = group[0]
+        left, right = order[g], order[g + s]
+        new = []
+        for p in left:
+            new.append(p)
+            if p + s <= group[-1]:
+                new.append(p + s)  # p hands the lower half of its panel (by work) to p+s
+        levels.append((s, group, list(left), list(right)))
+        order[g] = new
+        del order[g + s]
+    return levels, order[0]
+
+
+def tree_merge_distributed(rank, nparts, partial, send, recv, send_rows, bcast, row_weights, multiply, concat,
+                           gather=None):
+    """Step-doubling merge in which every product is row-panel sharded over the ranks of its subtree
+    AND STAYS DISTRIBUTED: the panels of an intermediate product are not gathered on the group
+    leader and scattered again one level up (tree_merge_panels), they are split in place.  For the
+    merge of the groups led by g (left operand) and g+s (right operand):
+      1. every rank that holds a panel of the right operand broadcasts it inside the group; all
+         ranks concatenate the panels (ascending rows) into the full right operand;
+      2. every rank p that holds a panel of the left operand keeps the upper half of it (by tiles)
+         and sends the lower half to rank p+s, which has just given its own panel away;
+      3. every rank multiplies its (half) panel by the right operand: a panel of the product.
+    Only the final product is gathered (on rank 0).  Per level: one broadcast per right-hand panel
+    and one point-to-point message per pair, all pairs at once.  Same association tree, same fold
+    order per output element: bit-identical to tree_merge and to the reference's rank-0 loop
+    (cu:569-571).  Callables as in tree_merge_panels; send_rows(obj, lo, hi, dst) moves block rows
+    [lo, hi), multiply(left, right, (lo, hi) or None); gather(held, order) (optional) -> list of the
+    panels in `order` on rank 0, None elsewhere."""
+    levels, final = panel_orders(nparts)
+    held = partial
+    trace = _phase_tracer(rank)
+    for s, group, left, right in levels:
+        if rank not in group:
+            continue
+        panels = [bcast(held if rank == q else None, q, group) for q in right]
+        right_full = panels[0] if len(panels) == 1 else concat(panels)
+        trace("s=%d right operand" % s)
+        if rank in left:
+            partner = rank + s
+            if partner <= group[-1]:
+                w = np.asarray(row_weights(held), dtype=np.int64)
+                c = np.cumsum(w)
+                mid = int(np.searchsorted(c, (c[-1] + 1) // 2, side="left")) + 1 if c.size and c[-1] > 0 else 0
+                send_rows(held, mid, w.size, partner)
+                trace("s=%d left half sent" % s)
+                held = multiply(held, right_full, (0, mid))
+            else:
+                held = multiply(held, right_full, None)
+        else:
+            mine = recv(rank - s)
+            trace("s=%d left half received" % s)
+            held = multiply(mine, right_full, None)
+        trace("s=%d panel product" % s)
+    if rank >= nparts:
+        return None
+    if gather is not None:  # all panels at once (GpuTransport.gather: one batch of receives instead of a loop)
+        parts = gather(held, final)
+        if rank != 0:
+            return None
+    else:
+        if rank != 0:
+            send(held, 0)
+            return None
+        parts = [held if r == 0 else recv(r) for r in final]
+    if len(final) == 1:
+        return held
+    trace("final gather")
+    out = concat(parts)
+    trace("final concat")
+    return out
+
+
 def device_row_weights(torch, mat):
     """Tiles per block row of a device matrix (the balance proxy for row panels)."""
     nbr = mat.device_view()[0]
@@ -307,3 +388,164 @@ class GroupBroadcaster:
             dist.broadcast(pl.colidx, src, group=grp)
             dist.broadcast(pl.vals, src, group=grp)
         return pl
+
+
+class GpuTransport:
+    """Moves bspgemm matrices between ranks over NCCL with as few launches and host waits as the
+    sizes allow: one 6-word header message, one packed body (rowptr | colidx | vals in ONE buffer,
+    8-byte aligned sections), one host wait per received message (the receiver has to read the
+    header to size the body).  The context must run on torch's current stream: the device-to-device
+    copies of the library, torch's slicing kernels and the NCCL calls are then ordered by the stream
+    and nothing else synchronises.  Provides the callables of tree_merge_distributed /
+    tree_merge_panels.  `sent` counts the bytes this rank put on the wire."""
+
+    def __init__(self, torch, dist, ctx, nparts):
+        self.torch, self.dist, self.ctx = torch, dist, ctx
+        self.sent = 0
+        self.groups = {}
+        self._rowptr_host = {}
+        for _, ranks in merge_groups(nparts):
+            key = tuple(ranks)
+            if key not in self.groups:  # new_group is collective over the whole world: same order everywhere
+                self.groups[key] = dist.new_group(ranks=ranks)
+
+    # ---- packing ---------------------------------------------------------------------------
+    @staticmethod
+    def _layout(nbr, nnzb, kk):
+        o_col = (4 * (nbr + 1) + 7) // 8 * 8
+        o_val = o_col + (4 * nnzb + 7) // 8 * 8
+        return o_col, o_val, o_val + 8 * nnzb * kk
+
+    class _Raw:
+        """Raw device memory as an object torch.as_tensor can wrap without copying."""
+
+        def __init__(self, ptr, nbytes):
+            self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+    def _views(self, mat):
+        """(header list, uint8 views of the matrix' rowptr / colidx / vals) -- no copy, no library call."""
+        torch = self.torch
+        rows, cols, k, nnzb = mat.info()
+        nbr, nbc, p_row, p_col, p_val = mat.device_view()
+        as_u8 = lambda ptr, n: torch.as_tensor(self._Raw(ptr, n), device="cuda") if n else torch.empty(0, dtype=torch.uint8, device="cuda")  # noqa: E731
+        return ([rows, cols, k, nbr, nbc, nnzb], as_u8(p_row, 4 * (nbr + 1)), as_u8(p_col, 4 * nnzb),
+                as_u8(p_val, 8 * nnzb * k * k))
+
+    def _export(self, mat):
+        torch = self.torch
+        hdr, v_row, v_col, v_val = self._views(mat)
+        nbr, nnzb, kk = hdr[3], hdr[5], hdr[2] * hdr[2]
+        o_col, o_val, total = self._layout(nbr, nnzb, kk)
+        body = torch.empty(max(total, 8), dtype=torch.uint8, device="cuda")
+        body[:v_row.numel()].copy_(v_row)
+        if nnzb:
+            body[o_col:o_col + v_col.numel()].copy_(v_col)
+            body[o_val:o_val + v_val.numel()].copy_(v_val)
+        return hdr, body
+
+    def host_rowptr(self, mat):
+        """rowptr of a device matrix on the host (one small download and one wait), cached per matrix."""
+        key = id(mat)
+        hit = self._rowptr_host.get(key)
+        if hit is not None and hit[0] is mat:
+            return hit[1]
+        _, v_row, _, _ = self._views(mat)
+        host = v_row.view(self.torch.int32).cpu().numpy()
+        self._rowptr_host = {key: (mat, host)}  # only the latest: the merge asks about one matrix at a time
+        return host
+
+    def row_weights(self, mat):
+        return np.diff(self.host_rowptr(mat))
+
+    def _pack_rows(self, mat, lo, hi):
+        torch = self.torch
+        hdr, v_row, v_col, v_val = self._views(mat)
+        nbr, kk = hdr[3], hdr[2] * hdr[2]
+        rp = self.host_rowptr(mat)
+        lo, hi = max(0, min(lo, nbr)), max(0, min(hi, nbr))
+        s0, s1 = int(rp[lo]), int(rp[max(hi, lo)])
+        n = s1 - s0
+        o_col, o_val, total = self._layout(nbr, n, kk)
+        body = torch.empty(max(total, 8), dtype=torch.uint8, device="cuda")
+        body[:4 * (nbr + 1)].view(torch.int32).copy_(torch.clamp(v_row.view(torch.int32), s0, s1) - s0)
+        if n:
+            body[o_col:o_col + 4 * n].copy_(v_col[4 * s0:4 * s1])
+            body[o_val:o_val + 8 * n * kk].copy_(v_val[8 * s0 * kk:8 * s1 * kk])
+        return hdr[:5] + [n], body
+
+    def _to_matrix(self, hdr, body):
+        rows, cols, k, nbr, nbc, nnzb = hdr
+        o_col, o_val, _ = self._layout(nbr, nnzb, k * k)
+        base = body.data_ptr()
+        return self.ctx.matrix_from_device_bcsr(rows, cols, k, nbr, nbc, nnzb, base, base + o_col if nnzb else 0,
+                                                base + o_val if nnzb else 0)
+
+    # ---- point to point --------------------------------------------------------------------
+    def _send(self, hdr, body, dst):
+        torch, dist = self.torch, self.dist
+        dist.send(torch.tensor(hdr, dtype=torch.int64, device="cuda"), dst)
+        dist.send(body, dst)
+        self.sent += body.numel() + 8 * HEADER_LEN
+
+    def send(self, mat, dst):
+        self._send(*self._export(mat), dst)
+
+    def send_rows(self, mat, lo, hi, dst):
+        self._send(*self._pack_rows(mat, lo, hi), dst)
+
+    def recv(self, src):
+        torch, dist = self.torch, self.dist
+        header = torch.empty(HEADER_LEN, dtype=torch.int64, device="cuda")
+        dist.recv(header, src)
+        hdr = [int(x) for x in header.cpu().tolist()]
+        total = self._layout(hdr[3], hdr[5], hdr[2] * hdr[2])[2]
+        body = torch.empty(max(total, 8), dtype=torch.uint8, device="cuda")
+        dist.recv(body, src)
+        return self._to_matrix(hdr, body)
+
+    # ---- broadcast inside a merge group ----------------------------------------------------------
+    def bcast(self, mat, src, ranks):
+        torch, dist = self.torch, self.dist
+        grp = self.groups[tuple(ranks)]
+        if mat is not None:
+            hdr, body = self._export(mat)
+            header = torch.tensor(hdr, dtype=torch.int64, device="cuda")
+            self.sent += body.numel() + 8 * HEADER_LEN
+        else:
+            header = torch.empty(HEADER_LEN, dtype=torch.int64, device="cuda")
+        dist.broadcast(header, src, group=grp)
+        if mat is not None:
+            dist.broadcast(body, src, group=grp)
+            return mat  # the owner keeps using its own copy
+        hdr = [int(x) for x in header.cpu().tolist()]
+        total = self._layout(hdr[3], hdr[5], hdr[2] * hdr[2])[2]
+        body = torch.empty(max(total, 8), dtype=torch.uint8, device="cuda")
+        dist.broadcast(body, src, group=grp)
+        return self._to_matrix(hdr, body)
+
+    # ---- all panels of the final product to rank 0 -------------------------------------------------
+    def gather(self, mat, order):
+        """Rank 0 posts the header receives of all peers as one batch, waits once, then posts all body
+        receives as one batch (the transfers overlap); the other ranks send header and body."""
+        torch, dist = self.torch, self.dist
+        rank = dist.get_rank()
+        if rank != 0:
+            if rank in order:
+                hdr, body = self._export(mat)
+                header = torch.tensor(hdr, dtype=torch.int64, device="cuda")
+                for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, header, 0), dist.P2POp(dist.isend, body, 0)]):
+                    w.wait()
+                self.sent += body.numel() + 8 * HEADER_LEN
+            return None
+        peers = [r for r in order if r != 0]
+        if not peers:
+            return [mat]
+        headers = torch.empty((len(peers), HEADER_LEN), dtype=torch.int64, device="cuda")
+        for w in dist.batch_isend_irecv([dist.P2POp(dist.irecv, headers[i], r) for i, r in enumerate(peers)]):
+            w.wait()
+        hdrs = [[int(x) for x in row] for row in headers.cpu().tolist()]
+        bodies = [torch.empty(max(self._layout(h[3], h[5], h[2] * h[2])[2], 8), dtype=torch.uint8, device="cuda") for h in hdrs]
+        for w in dist.batch_isend_irecv([dist.P2POp(dist.irecv, bodies[i], r) for i, r in enumerate(peers)]):
+            w.wait()
+        got = {r: self._to_matrix(hdrs[i], bodies[i]) for i, r in enumerate(peers)}
+        return [mat if r == 0 else got[r] for r in order]

@@ -73,7 +73,8 @@ def _worker(rank, world, port, n_mats, k, G, outdir, panels=False):
         recv = lambda src: _payload_to_omat(bsp_dist.recv_payload(dist, torch, src, "cpu"))  # noqa: E731
         if panels:
             gb = bsp_dist.GroupBroadcaster(dist, torch, len(parts), "cpu")
-            res = bsp_dist.tree_merge_panels(
+            merge = bsp_dist.tree_merge_distributed if panels == "dist" else bsp_dist.tree_merge_panels
+            res = merge(
                 rank, len(parts), partial, send, recv,
                 send_rows=lambda m, lo, hi, dst: bsp_dist.send_payload(
                     dist, bsp_dist.slice_rows_payload(torch, _omat_to_payload(m), lo, hi), dst),
@@ -91,7 +92,8 @@ def _worker(rank, world, port, n_mats, k, G, outdir, panels=False):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,n_mats,panels", [(2, 5, False), (2, 1, False), (3, 7, False), (2, 5, True), (4, 9, True)])
+@pytest.mark.parametrize("world,n_mats,panels", [(2, 5, False), (2, 1, False), (3, 7, False), (2, 5, True), (4, 9, True),
+                                                 (2, 5, "dist"), (3, 7, "dist"), (4, 9, "dist"), (2, 1, "dist")])
 def test_tree_merge_over_gloo_matches_rank_oracle(world, n_mats, panels):
     k, G = 2, 8
     with tempfile.TemporaryDirectory() as d:

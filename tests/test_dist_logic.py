@@ -40,3 +40,26 @@ def test_balanced_panels():
     loads = [w[b[i]:b[i + 1]].sum() for i in range(2)]
     assert max(loads) <= 104
     assert bsp_dist.balanced_panels(np.ones(10), 5) == [0, 2, 4, 6, 8, 10]
+
+
+@pytest.mark.parametrize("n", list(range(1, 18)))
+def test_panel_orders_cover_every_rank_once(n):
+    """tree_merge_distributed: after every level the panels of a group's product are held by
+    exactly the ranks of the group, each once; a rank hands rows only to rank+s inside its group."""
+    levels, final = bsp_dist.panel_orders(n)
+    assert sorted(final) == list(range(n)) and final[0] == 0
+    assert [(s, g) for s, g, _, _ in levels] == bsp_dist.merge_groups(n)
+    seen = {r: [r] for r in range(n)}
+    for s, group, left, right in levels:
+        g = group[0]
+        assert left == seen[g] and right == seen[g + s]
+        assert sorted(left + right) == group
+        assert all(q - s in left for q in right)       # every right-hand rank has a partner that feeds it
+        new = []
+        for p in left:
+            new.append(p)
+            if p + s in right:
+                new.append(p + s)
+        seen[g] = new
+        del seen[g + s]
+    assert seen == {0: final}

@@ -45,7 +45,9 @@ rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(rank)
 dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
 k, G, n = 4, 40, 9
-ctx = bspgemm.Context(rank)
+stream = torch.cuda.Stream()
+torch.cuda.set_stream(stream)   # GpuTransport needs the context on torch's current stream
+ctx = bspgemm.Context(rank, stream=stream.cuda_stream)
 parts = bsp_dist.split_chain(n, world)
 s, e = parts[rank]
 mats = [ctx.matrix_from_coo(*bsp_gen.random_matrix(G * k, G * k, k, 0.08, 8100 + i, "edgy")) for i in range(s, e + 1)]
@@ -60,6 +62,12 @@ if sys.argv[4] == "panels":
         lambda m, src, grp: bsp_dist.payload_to_matrix(torch, ctx, gb.bcast(bsp_dist.matrix_to_payload(torch, m) if m is not None else None, src, grp)),
         lambda m: bsp_dist.device_row_weights(torch, m),
         lambda a, b, rng: ctx.helper(a, b, panel=rng), ctx.concat_panels)
+elif sys.argv[4] == "distributed":
+    tp = bsp_dist.GpuTransport(torch, dist, ctx, len(parts))
+    res = bsp_dist.tree_merge_distributed(rank, len(parts), partial, tp.send, tp.recv, tp.send_rows, tp.bcast,
+                                          tp.row_weights, lambda a, b, rng: ctx.helper(a, b, panel=rng), ctx.concat_panels,
+                                          gather=tp.gather if len(sys.argv) > 5 else None)
+    assert tp.sent > 0
 else:
     res = bsp_dist.tree_merge(rank, len(parts), partial, lambda a, b: ctx.helper(a, b), send, recv)
 if rank == 0:
@@ -70,7 +78,7 @@ dist.destroy_process_group()
 
 
 @pytest.mark.skipif("_ngpu() < 2")
-@pytest.mark.parametrize("mode", ["rank0", "panels"])
+@pytest.mark.parametrize("mode", ["rank0", "panels", "distributed", "distributed+gather"])
 def test_nccl_tree_merge_two_ranks(mode):
     k, G, n = 4, 40, 9
     pkg = os.path.dirname(bspgemm.__file__)
@@ -80,7 +88,7 @@ def test_nccl_tree_merge_two_ranks(mode):
         out = os.path.join(d, "matrix")
         p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                             "--master-addr", "127.0.0.1", "--master-port", "29611", script, pkg,
-                            os.path.join(util.ROOT, "oracle"), out, mode], stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+                            os.path.join(util.ROOT, "oracle"), out] + mode.split("+"), stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
         assert p.returncode == 0, p.stderr.decode()[-3000:]
         mats = [orc.OMat.from_coo(*bsp_gen.random_matrix(G * k, G * k, k, 0.08, 8100 + i, "edgy")) for i in range(n)]
         want = orc.chain(mats, ranks=2)[0].prune_zero()
