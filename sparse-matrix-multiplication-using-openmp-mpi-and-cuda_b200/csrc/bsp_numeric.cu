@@ -575,8 +575,10 @@ int build_schedule(bsp_ctx *ctx, const bsp_mat *B, const bsp_symbolic_out *sym, 
     // single over-long tile next to empty neighbours (dense chain levels fold 100+ pairs per tile)
     int Q = tn.Q;
     if (!tn.q_forced && sym->nnzb_c > 0) {
-        const int64_t avg4 = 4 * (sym->nprod / sym->nnzb_c);
-        if (avg4 > Q) Q = (int)(avg4 > 8192 ? 8192 : avg4);
+        // ten tiles' worth, at most 2048 (chain top product, 105 pairs per tile: Q = 420 -> 6.55 ms,
+        // 1024 -> 5.98 ms, 2048 -> 6.1 ms, 4096 -> 7.2 ms)
+        const int64_t avg10 = 10 * (sym->nprod / sym->nnzb_c);
+        if (avg10 > Q) Q = (int)(avg10 > 2048 ? 2048 : avg10);
     }
     if (!tn.q_forced && tile_bytes >= 2048) Q = Q / 4 > 8 ? Q / 4 : 8; // big tiles: a step is 8-64x the work
     cs->nseg = (int64_t)nbr * npanels;

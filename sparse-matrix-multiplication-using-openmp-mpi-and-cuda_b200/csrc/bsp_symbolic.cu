@@ -550,6 +550,135 @@ sym_fill_global_kernel(const int32_t *__restrict__ rowlist, const int32_t *__res
     }
 }
 
+// ---- fill, rows with many pairs per output tile: bit matrix instead of ordered placement ----------
+// Chain levels (banded factors: every tile of a row of C folds 17..105 pairs) spend their time in the
+// ordered placement above: one barrier per A entry, half the CTA idle, 6..50 products per ns.  For a
+// row with T output tiles and nA entries in its A row this kernel keeps the T x nA bit matrix
+// M[t][e] = "A entry e contributes to tile t" in shared memory.  Every product sets its bit (any
+// order); the pairs of tile t are then its set bits in ascending e, which IS ascending inner index j,
+// so a product's slot is a popcount prefix and the last pair of a tile is its highest bit.  No per-
+// product shared memory (pairs go straight to global memory), so the row may be of any length: it
+// serves rows of every class whose matrix fits (two sizes, DENSE_M0 / DENSE_M1 words).
+constexpr int DENSE_THREADS = 512;
+constexpr int DENSE_M0 = 6 * 1024;   // 24 KB: several CTAs per SM
+constexpr int DENSE_M1 = 40 * 1024;  // 160 KB: one CTA per SM
+constexpr int DENSE_MIN_RATIO = 8;   // rows with at least this many tile products per output tile
+
+__host__ __device__ inline int dense_row_words(int nA) { return ((nA + 31) / 32) | 1; } // odd stride: no bank conflicts
+
+// shared-memory words a row needs next to the column bitmap: the T x W bit matrix and T+1 tile starts
+__host__ __device__ inline int dense_need_words(int T, int nA) { return T * (dense_row_words(nA) + 1) + 1; }
+
+__host__ __device__ inline size_t dense_smem_bytes(int words, int mcap)
+{
+    return 8 * (size_t)words + 4 * (size_t)mcap + 16; // bitmap + ranks, then M and the tile starts
+}
+
+__global__ void __launch_bounds__(DENSE_THREADS)
+sym_fill_dense_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
+                      const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
+                      const int32_t *__restrict__ b_colidx, int words, int mcap,
+                      const int32_t *__restrict__ c_rowptr, const int64_t *__restrict__ row_prod_ptr,
+                      int32_t *__restrict__ c_colidx, int64_t *__restrict__ pair_ptr, int2 *__restrict__ pairs)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ int sm33[33];
+    uint32_t *bm = smem;
+    uint32_t *wrank = bm + words;
+    uint32_t *M = wrank + words;          // [T * W]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = DENSE_THREADS / 32;
+    const int row = rowlist[blockIdx.x];
+    const int cbase = c_rowptr[row], T = c_rowptr[row + 1] - cbase;
+    const int64_t pbase = row_prod_ptr[row];
+    const int a0 = a_rowptr[row], nA = a_rowptr[row + 1] - a0;
+    const int W = dense_row_words(nA);
+    int *tstart = (int *)(M + T * W);     // [T + 1]; T * (W + 1) + 1 <= mcap by classification
+    (void)mcap;
+    for (int w = tid; w < words; w += DENSE_THREADS) bm[w] = 0u;
+    for (int x = tid; x < T * W; x += DENSE_THREADS) M[x] = 0u;
+    __syncthreads();
+    // 1. column bitmap of the row
+    for (int e = warp; e < nA; e += nwarp) {
+        const int j = a_colidx[a0 + e];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            atomicOr(&bm[c >> 5], 1u << (c & 31));
+        }
+    }
+    __syncthreads();
+    // 2. rank table + sorted colidx of the C row
+    int carry = 0;
+    for (int w0 = 0; w0 < words; w0 += DENSE_THREADS) {
+        const int w = w0 + tid;
+        const uint32_t bits = w < words ? bm[w] : 0u;
+        int tot;
+        const int ex = block_excl_scan_i32(__popc(bits), sm33, &tot);
+        if (w < words) {
+            wrank[w] = (uint32_t)(carry + ex);
+            uint32_t b = bits;
+            int o = cbase + carry + ex;
+            while (b) {
+                const int bit = __ffs(b) - 1;
+                b &= b - 1;
+                c_colidx[o++] = w * 32 + bit;
+            }
+        }
+        carry += tot;
+    }
+    __syncthreads();
+    // 3. every product sets its bit
+    for (int e = warp; e < nA; e += nwarp) {
+        const int j = a_colidx[a0 + e];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        const uint32_t ebit = 1u << (e & 31);
+        const int ew = e >> 5;
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+            atomicOr(&M[t * W + ew], ebit);
+        }
+    }
+    __syncthreads();
+    // 4. pairs per tile = popcount of its row of M; scan -> first slot of every tile
+    carry = 0;
+    for (int t0 = 0; t0 < T; t0 += DENSE_THREADS) {
+        const int t = t0 + tid;
+        int cnt = 0;
+        if (t < T)
+            for (int w = 0; w < W; w++) cnt += __popc(M[t * W + w]);
+        int tot;
+        const int ex = block_excl_scan_i32(cnt, sm33, &tot);
+        if (t < T) {
+            tstart[t] = carry + ex;
+            pair_ptr[(size_t)cbase + t] = pbase + carry + ex;
+        }
+        carry += tot;
+    }
+    if (tid == 0) tstart[T] = carry;
+    __syncthreads();
+    // 5. slot of a product = first slot of its tile + number of set bits below its own
+    for (int e = warp; e < nA; e += nwarp) {
+        const int j = a_colidx[a0 + e];
+        if (j >= b_nbr) continue;
+        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+        const uint32_t below = (1u << (e & 31)) - 1u;
+        const int ew = e >> 5;
+        for (int q = b0 + lane; q < b1; q += 32) {
+            const int c = b_colidx[q];
+            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+            const uint32_t *Mt = M + t * W;
+            int r = __popc(Mt[ew] & below);
+            for (int w = 0; w < ew; w++) r += __popc(Mt[w]);
+            const int pos = tstart[t] + r;
+            const int last = (pos + 1 == tstart[t + 1]) ? (int)0x80000000 : 0;
+            pairs[pbase + pos] = make_int2(a0 + e, q | last);
+        }
+    }
+}
+
 // ---- fill, very long rows: several CTAs per row, one phase per launch --------------------------------
 // sym_fill_global_kernel gives a row that does not fit in shared memory ONE CTA, which handles 0.3-0.4
 // tile products per ns: fine for 10^4..10^5 products per row (all rows run side by side), but an R-MAT
@@ -841,13 +970,15 @@ sym_fill_tiny_kernel(const int32_t *__restrict__ rowlist, int nrows, const int32
 // ---- rows -> capacity classes -----------------------------------------------------------------
 // class c rows go to lists[c * nbr ...]; counts[c] = rows in class c.  A row with P tile
 // products fits class c when P <= caps[c]; larger than every cap -> class NCLASS-1 (global).
-constexpr int NCLASS = 6; // 0: tiny rows (warp + sort), 1..3: shared-memory CTA classes, 4: global-memory CTA,
+constexpr int NCLASS = 8; // 6, 7: rows with many pairs per tile whose bit matrix fits DENSE_M0 / DENSE_M1 words;
+                          // 0: tiny rows (warp + sort), 1..3: shared-memory CTA classes, 4: global-memory CTA,
                           // 5: rows so long that one CTA would be the tail of the pass -> multi-launch path
 
 __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowptr,
                                      const int32_t *__restrict__ row_cnt, const int32_t *__restrict__ row_prod,
                                      int cap0, int cap1, int cap2, int tcap0, int tcap1, int tcap2, int acap,
-                                     int tiny_ok, int hv_min, int32_t *__restrict__ lists, int32_t *__restrict__ counts)
+                                     int tiny_ok, int hv_min, int dense_ok, int32_t *__restrict__ lists,
+                                     int32_t *__restrict__ counts)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nbr || row_cnt[row] == 0) return;
@@ -857,6 +988,11 @@ __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowp
     if (nA > acap) cls = 4;                                  // A row too long for the shared-memory entry table
     if (tiny_ok && P <= TINY_P && nA <= TINY_A) cls = 0;     // warp-per-row sort
     if (cls == 4 && P > hv_min) cls = 5;                     // spread over the whole GPU
+    if (dense_ok && cls != 0 && P >= DENSE_MIN_RATIO * T) {  // many pairs per tile: bit-matrix placement
+        const int mw = T <= DENSE_M1 ? dense_need_words(T, nA) : DENSE_M1 + 1;
+        if (mw <= DENSE_M0) cls = 6;
+        else if (mw <= DENSE_M1) cls = 7;
+    }
     const int slot = atomicAdd(&counts[cls], 1);
     lists[(size_t)cls * nbr + slot] = row;
 }
@@ -977,6 +1113,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     // (measured: chain top product, 66 k products per row: 3.3 ms against 38 ms).  BSP_HV_MIN_P is a test hook.
     int hv_min = 1 << 18;
     if (const char *e = getenv("BSP_HV_MIN_P")) { const int v = atoi(e); if (v > 0) hv_min = v; }
+    const int dense_ok = getenv("BSP_SYM_NO_DENSE") ? 0 : 1; // comparison hook: rows keep their capacity class
     // the tiny-row kernel packs the block column into 27 bits; BSP_SYM_CAPS (a test hook) also switches it off
     const int tiny_ok = (B->nbc < (1 << 27) && !getenv("BSP_SYM_CAPS")) ? 1 : 0;
     for (int c = 0; c < 3; c++) {
@@ -1005,7 +1142,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         }
         classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, A->rowptr, row_cnt, row_prod, caps[0],
                                                                         caps[1], caps[2], tcaps[0], tcaps[1], tcaps[2],
-                                                                        acap, tiny_ok, hv_min, lists, counts);
+                                                                        acap, tiny_ok, hv_min, dense_ok, lists, counts);
         BSP_LAUNCH_CHECK(ctx);
     }
     bsp_trace_mark(ctx, "sym_count");
@@ -1083,6 +1220,16 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         sym_fill_global_kernel<<<ncls[4], FILLG_THREADS, bitmap_bytes, ctx->stream>>>(
             lists + (size_t)4 * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, out->c_rowptr,
             row_prod_ptr, out->c_colidx, (unsigned long long *)out->pair_ptr, out->pairs);
+        BSP_LAUNCH_CHECK(ctx);
+    }
+    for (int c = 6; c <= 7; c++) {
+        if (ncls[c] == 0) continue;
+        const int mcap = c == 6 ? DENSE_M0 : DENSE_M1;
+        const size_t bytes = dense_smem_bytes(words, mcap);
+        BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        sym_fill_dense_kernel<<<ncls[c], DENSE_THREADS, bytes, ctx->stream>>>(
+            lists + (size_t)c * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, mcap, out->c_rowptr,
+            row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
     if (ncls[5] > 0) BSP_TRY(fill_heavy_rows(ctx, A, B, lists + (size_t)5 * nbr, ncls[5], words, out, row_prod_ptr));

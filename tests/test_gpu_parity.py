@@ -442,7 +442,7 @@ def test_very_long_rows_multi_launch_fill(ctx, monkeypatch):
     multi-launch path: global bitmaps, atomic counts and cursors, then a sort of every tile's pairs
     by inner index.  Covers tile lists of 1..32 pairs (warp sort), hundreds (shared-memory sort) and
     > 8192 (global scratch sort); 'edgy' values make any pair out of order visible (the fold is order
-    dependent).  The one-CTA kernel (default at these sizes) must give the same bits."""
+    dependent).  The one-CTA kernel and the bit-matrix kernel (default for these rows) must give the same bits."""
     k, G = 4, 600
     rows, cols, _, br, bc, v = bsp_gen.random_matrix(G * k, G * k, k, 0.01, 500, "edgy")
     hub_r = np.repeat(np.array([3, 77, 599], np.int32), G)
@@ -452,8 +452,7 @@ def test_very_long_rows_multi_launch_fill(ctx, monkeypatch):
     b = bsp_gen.random_matrix(G * k, G * k, k, 0.3, 502, "edgy")
     want, _ = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b), threads=8)
     s0, s1 = bspgemm.Stats(), bspgemm.Stats()
-    one_cta = ctx.helper(dev(ctx, a), dev(ctx, b), stats=s0)
-    assert_same(one_cta, want)
+    assert_same(ctx.helper(dev(ctx, a), dev(ctx, b)), want)      # default: the hub rows fit the bit-matrix fill
     # one output tile with 9000 pairs: a full row of A (k = 1) times two full columns of B
     n = 9000
     a1 = (1, n, 1, np.zeros(n, np.int32), np.arange(n, dtype=np.int32), bsp_gen.values(510, n, "edgy"))
@@ -462,8 +461,40 @@ def test_very_long_rows_multi_launch_fill(ctx, monkeypatch):
     want1, nprod = orc.multiply(orc.OMat.from_coo(*a1), orc.OMat.from_coo(*b1))
     assert nprod == 2 * n
     assert_same(ctx.helper(dev(ctx, a1), dev(ctx, b1)), want1)
+    monkeypatch.setenv("BSP_SYM_NO_DENSE", "1")
+    one_cta = ctx.helper(dev(ctx, a), dev(ctx, b), stats=s0)
+    assert_same(one_cta, want)
+    assert_same(ctx.helper(dev(ctx, a1), dev(ctx, b1)), want1)
     monkeypatch.setenv("BSP_HV_MIN_P", "10000")
     multi = ctx.helper(dev(ctx, a), dev(ctx, b), stats=s1)
     assert_same(multi, want)
     assert s1.launches > s0.launches                 # the three hub rows (108 000 products each) took the other path
     assert_same(ctx.helper(dev(ctx, a1), dev(ctx, b1)), want1)
+
+
+def test_banded_chain_bit_matrix_fill(monkeypatch):
+    """The chain workload of bench.py at test size: banded factors, every output tile of the upper
+    levels folds tens of pairs, so the rows go through the bit-matrix fill (both sizes of it: the
+    last levels need more than 24 KB).  Against the oracle's tree, and against the same run with the
+    bit-matrix classes switched off (BSP_SYM_NO_DENSE=1)."""
+    k, G, n = 4, 512, 32
+    mats = []
+    for i in range(n):
+        br, bc = bsp_gen.banded_pattern(G, 4, 0.5, 7000 + i)
+        mats.append((G * k, G * k, k, br, bc, bsp_gen.values(7000 + i, br.size * k * k, "edgy" if i % 5 == 0 else "u64")))
+    want, nprod = orc.chain([orc.OMat.from_coo(*m) for m in mats])
+    with bspgemm.Context(0) as c1:
+        st = bspgemm.Stats()
+        got = c1.helper2([c1.matrix_from_coo(*m) for m in mats], stats=st)
+        assert_same(got, want)
+        assert st.nprod == nprod
+        sums = got.checksum()
+        # the top product alone, whole and as panels
+        left, right = c1.helper2([c1.matrix_from_coo(*m) for m in mats[:16]]), c1.helper2([c1.matrix_from_coo(*m) for m in mats[16:]])
+        top = c1.helper(left, right)
+        assert top.checksum() == sums
+        parts = [c1.helper(left, right, panel=(lo, hi)) for lo, hi in ((0, 100), (100, 101), (101, G))]
+        assert c1.concat_panels(parts).checksum() == sums
+    monkeypatch.setenv("BSP_SYM_NO_DENSE", "1")
+    with bspgemm.Context(0) as c2:
+        assert c2.helper2([c2.matrix_from_coo(*m) for m in mats]).checksum() == sums
