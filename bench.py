@@ -38,7 +38,7 @@ WORKLOADS = {
     "k32": (65536, 32, 0.02, "u64"),   # the tile size of the reference's own published numbers (report.pdf)
 }
 # DRAM bytes of one numeric-kernel launch from the committed `ncu --set full` capture (not measured live)
-NCU_TRAFFIC_BYTES = {("cfg2", 8): 30182856000 + 19197000000}
+NCU_TRAFFIC_BYTES = {("cfg2", 8): 29629984000 + 19178306000}
 METRIC = "spgemm_useful_gflops"
 UNIT = "GFLOP/s"
 
@@ -597,7 +597,7 @@ def main():
                 "roofline": {"bound": "hbm", "kernel": "numeric pass (tile multiply-accumulate)", "achieved": ach,
                              "peak": peak, "unit": "GB/s", "frac": ach / peak,
                              "traffic": NCU_TRAFFIC_BYTES.get((args.workload, world == 1 and st.numeric_path)),
-                             "traffic_source": "profiles/r01_ncu_full_v5_raw.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
+                             "traffic_source": "profiles/r01_ncu_full_v11_numeric_raw.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
                              "algorithmic_bytes": alg, "peak_source": peak_src,
                              "useful_u64_mac_per_s": k ** 3 * st.nprod / (k_ms * 1e-3)},
                 "roofline_symbolic": {"bound": "hbm", "achieved": sb / (s_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
