@@ -159,27 +159,25 @@ int batched_level(bsp_ctx *ctx, const std::vector<bsp_mat *> &as, const std::vec
     bsp_mat_free(ctx, B);
     if (rc != BSP_OK) { bsp_mat_free(ctx, C); return rc; }
     // row pointers of the stacked product at the block boundaries -> tile ranges of the parts
-    std::vector<int32_t> bounds(m + 1);
+    std::vector<int32_t> bounds(m + 1), brow(m + 1);
     {
         int32_t row = 0;
         for (int i = 0; i <= m; i++) {
-            rc = cudaMemcpyAsync(&bounds[i], C->rowptr + row, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream) == cudaSuccess
-                     ? BSP_OK : BSP_ERR_CUDA;
-            if (rc != BSP_OK) break;
+            brow[i] = row;
             if (i < m) row += as[i]->nbr;
         }
-        if (rc == BSP_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = BSP_ERR_CUDA;
+        rc = bsp_gather_i32_to_host(ctx, C->rowptr, brow.data(), m + 1, bounds.data());
     }
-    int32_t row = 0;
+    std::vector<int64_t> toff(m);
     for (int i = 0; i < m && rc == BSP_OK; i++) {
         bsp_mat *P = nullptr;
         rc = new_empty_like(ctx, as[i]->rows, bs[i]->cols, k, as[i]->nbr, bs[i]->nbc, &P, esize);
         if (rc == BSP_OK) rc = fill(P, bounds[i + 1] - bounds[i]);
-        if (rc == BSP_OK) rc = bsp_split_rows_device(ctx, C, row, bounds[i], P);
         if (rc != BSP_OK) { bsp_mat_free(ctx, P); break; }
+        toff[i] = bounds[i];
         cs->push_back(P);
-        row += as[i]->nbr;
     }
+    if (rc == BSP_OK) rc = bsp_split_rows_device(ctx, C, m, brow.data(), toff.data(), cs->data());
     bsp_mat_free(ctx, C);
     if (rc != BSP_OK) {
         if (rc == BSP_ERR_CUDA) snprintf(ctx->err, sizeof(ctx->err), "batched chain level: CUDA copy failed");

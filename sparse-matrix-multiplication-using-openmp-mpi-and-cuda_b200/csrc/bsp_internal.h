@@ -179,7 +179,9 @@ int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m);
 int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bsp_mat *out);
 int bsp_stack_rows_device(bsp_ctx *ctx, const bsp_mat *const *mats, int n, const int32_t *shifts, const int32_t *limits,
                           int32_t sentinel, bsp_mat *out);
-int bsp_split_rows_device(bsp_ctx *ctx, const bsp_mat *big, int32_t row_off, int64_t tile_off, bsp_mat *part);
+int bsp_split_rows_device(bsp_ctx *ctx, const bsp_mat *big, int n, const int32_t *row_off, const int64_t *tile_off,
+                          bsp_mat *const *parts);
+int bsp_gather_i32_to_host(bsp_ctx *ctx, const int32_t *src, const int32_t *idx_host, int n, int32_t *dst_host);
 int bsp_expand_rows(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_brow);
 int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t esize, int64_t nnzb,
                    const int32_t *d_brow, const int32_t *d_bcol, const void *d_vals,

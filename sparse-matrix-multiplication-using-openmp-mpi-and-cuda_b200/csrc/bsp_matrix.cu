@@ -310,28 +310,117 @@ int bsp_concat_panels_device(bsp_ctx *ctx, bsp_mat *const *panels, int32_t n, bs
 // own B_i is replaced by a sentinel beyond the stacked B so that it cannot hit B_{i+1}.
 namespace {
 
-__global__ void stack_rowptr_kernel(const int32_t *__restrict__ src, int32_t n_rows, int32_t tile_off,
-                                    int32_t *__restrict__ dst /* already offset to this block's first row */, int last)
+// Building the stacks and cutting the result used to cost 9 launches or copies per product (about
+// 1.5 ms of API calls for a level of 32 products).  Here the parts are described by a table passed BY
+// VALUE as a kernel argument, every thread finds its part by a binary search in that table, and a
+// level costs two launches per stack or split whatever the number of products.
+constexpr int STACK_MAX = 32; // parts per launch (longer levels take several launches)
+
+struct stack_table {
+    int n;
+    const int32_t *rowptr[STACK_MAX];
+    const int32_t *colidx[STACK_MAX];
+    const uint32_t *vals[STACK_MAX];
+    int32_t shift[STACK_MAX], limit[STACK_MAX];
+    int32_t row_off[STACK_MAX + 1];   // first row of part i, relative to the first part of this launch
+    int64_t tile_off[STACK_MAX + 1];  // first tile of part i in the stack (absolute)
+};
+
+struct split_table {
+    int n;
+    int32_t *rowptr[STACK_MAX];
+    int32_t *colidx[STACK_MAX];
+    uint32_t *vals[STACK_MAX];
+    int32_t row_off[STACK_MAX + 1];   // first row of part i in the big matrix
+    int64_t tile_off[STACK_MAX + 1];  // first tile of part i in the big matrix
+};
+
+template <typename T, typename V>
+__device__ __forceinline__ int find_part(const T *off, int n, V x) // last i < n with off[i] <= x
 {
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r < n_rows + (last ? 1 : 0)) dst[r] = src[r] + tile_off;
+    int lo = 0, hi = n;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if ((V)off[mid] <= x) lo = mid; else hi = mid;
+    }
+    return lo;
 }
 
-__global__ void stack_colidx_kernel(const int32_t *__restrict__ src, int64_t n, int32_t shift, int32_t limit,
-                                    int32_t sentinel, int32_t *__restrict__ dst)
+// row pointers and column indices of the stack (dst_rowptr / dst_colidx point at the first row / tile of this launch)
+__global__ void stack_meta_kernel(const __grid_constant__ stack_table tb, int32_t sentinel, int closing,
+                                  int32_t *__restrict__ dst_rowptr, int32_t *__restrict__ dst_colidx)
 {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) {
-        const int32_t j = src[i];
-        dst[i] = (limit >= 0 && j >= limit) ? sentinel : j + shift;
+    const int rows = tb.row_off[tb.n];
+    const int64_t tiles = tb.tile_off[tb.n] - tb.tile_off[0];
+    const int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (x < rows) {
+        const int i = find_part(tb.row_off, tb.n, (int)x);
+        dst_rowptr[x] = tb.rowptr[i][x - tb.row_off[i]] + (int32_t)tb.tile_off[i];
+    } else if (x == rows) {
+        if (closing) dst_rowptr[rows] = (int32_t)tb.tile_off[tb.n];
+    } else if (x - rows - 1 < tiles) {
+        const int64_t y = x - rows - 1 + tb.tile_off[0];
+        const int i = find_part(tb.tile_off, tb.n, y);
+        const int32_t j = tb.colidx[i][y - tb.tile_off[i]];
+        dst_colidx[y - tb.tile_off[0]] = (tb.limit[i] >= 0 && j >= tb.limit[i]) ? sentinel : j + tb.shift[i];
     }
 }
 
-__global__ void split_rowptr_kernel(const int32_t *__restrict__ src /* at the block's first row */, int32_t n_rows,
-                                    int32_t tile_off, int32_t *__restrict__ dst)
+// tile values of the stack, `units` pieces of VEC words per tile (dst points at the first tile of this launch)
+template <int VEC>
+__global__ void stack_vals_kernel(const __grid_constant__ stack_table tb, int units, uint32_t *__restrict__ dst)
 {
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r <= n_rows) dst[r] = src[r] - tile_off;
+    const int64_t total = (tb.tile_off[tb.n] - tb.tile_off[0]) * units;
+    for (int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; x < total; x += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t t = x / units + tb.tile_off[0];
+        const int i = find_part(tb.tile_off, tb.n, t);
+        const int64_t local = x - (tb.tile_off[i] - tb.tile_off[0]) * units;
+        if (VEC == 4) reinterpret_cast<uint4 *>(dst)[x] = reinterpret_cast<const uint4 *>(tb.vals[i])[local];
+        else dst[x] = tb.vals[i][local];
+    }
+}
+
+// the reverse: block rows [row_off[i], row_off[i+1]) of `big` become part i
+__global__ void split_meta_kernel(const __grid_constant__ split_table tb, const int32_t *__restrict__ big_rowptr,
+                                  const int32_t *__restrict__ big_colidx)
+{
+    const int rows = tb.row_off[tb.n] - tb.row_off[0];
+    const int64_t tiles = tb.tile_off[tb.n] - tb.tile_off[0];
+    const int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (x < rows + tb.n) { // part i has nbr_i + 1 row pointers: entry x of the concatenation of those lists
+        int lo = 0, hi = tb.n; // last i with row_off[i] - row_off[0] + i <= x
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (tb.row_off[mid] - tb.row_off[0] + mid <= x) lo = mid; else hi = mid;
+        }
+        const int r = (int)x - (tb.row_off[lo] - tb.row_off[0] + lo);
+        tb.rowptr[lo][r] = big_rowptr[tb.row_off[lo] + r] - (int32_t)tb.tile_off[lo];
+    } else if (x - rows - tb.n < tiles) {
+        const int64_t y = x - rows - tb.n + tb.tile_off[0];
+        const int i = find_part(tb.tile_off, tb.n, y);
+        tb.colidx[i][y - tb.tile_off[i]] = big_colidx[y];
+    }
+}
+
+template <int VEC>
+__global__ void split_vals_kernel(const __grid_constant__ split_table tb, int units, const uint32_t *__restrict__ big_vals)
+{
+    const int64_t total = (tb.tile_off[tb.n] - tb.tile_off[0]) * units;
+    const int64_t base = tb.tile_off[0] * units;
+    for (int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; x < total; x += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t t = x / units + tb.tile_off[0];
+        const int i = find_part(tb.tile_off, tb.n, t);
+        const int64_t local = x - (tb.tile_off[i] - tb.tile_off[0]) * units;
+        if (VEC == 4) reinterpret_cast<uint4 *>(tb.vals[i])[local] = reinterpret_cast<const uint4 *>(big_vals)[base + x];
+        else tb.vals[i][local] = big_vals[base + x];
+    }
+}
+
+__global__ void gather_i32_kernel(const int32_t *__restrict__ src, const int32_t *__restrict__ idx, int n,
+                                  int32_t *__restrict__ dst)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[idx[i]];
 }
 
 } // namespace
@@ -340,39 +429,89 @@ __global__ void split_rowptr_kernel(const int32_t *__restrict__ src /* at the bl
 int bsp_stack_rows_device(bsp_ctx *ctx, const bsp_mat *const *mats, int n, const int32_t *shifts, const int32_t *limits,
                           int32_t sentinel, bsp_mat *out /* arrays allocated, nbr / nnzb set */)
 {
-    const size_t tb = (size_t)out->k * out->k * out->esize;
+    const int kk = out->k * out->k * (out->esize / 4); // 32-bit words per tile
+    const int vec = (kk % 4 == 0) ? 4 : 1;
+    const int units = kk / vec;
+    if (n == 0) BSP_CUDA(ctx, cudaMemsetAsync(out->rowptr, 0, sizeof(int32_t), ctx->stream));
     int64_t tile_off = 0;
     int32_t row_off = 0;
-    for (int i = 0; i < n; i++) {
-        const bsp_mat *m = mats[i];
-        stack_rowptr_kernel<<<blocks_for((int64_t)m->nbr + 1, 256), 256, 0, ctx->stream>>>(
-            m->rowptr, m->nbr, (int32_t)tile_off, out->rowptr + row_off, i == n - 1);
-        BSP_LAUNCH_CHECK(ctx);
-        if (m->nnzb) {
-            stack_colidx_kernel<<<blocks_for(m->nnzb, 256), 256, 0, ctx->stream>>>(
-                m->colidx, m->nnzb, shifts ? shifts[i] : 0, limits ? limits[i] : -1, sentinel, out->colidx + tile_off);
-            BSP_LAUNCH_CHECK(ctx);
-            BSP_CUDA(ctx, cudaMemcpyAsync((char *)out->vals + (size_t)tile_off * tb, m->vals, (size_t)m->nnzb * tb,
-                                          cudaMemcpyDeviceToDevice, ctx->stream));
+    for (int i0 = 0; i0 < n; i0 += STACK_MAX) {
+        stack_table tb;
+        tb.n = n - i0 < STACK_MAX ? n - i0 : STACK_MAX;
+        int32_t r = 0;
+        int64_t t = tile_off;
+        for (int i = 0; i < tb.n; i++) {
+            const bsp_mat *m = mats[i0 + i];
+            tb.rowptr[i] = m->rowptr; tb.colidx[i] = m->colidx; tb.vals[i] = (const uint32_t *)m->vals;
+            tb.shift[i] = shifts ? shifts[i0 + i] : 0;
+            tb.limit[i] = limits ? limits[i0 + i] : -1;
+            tb.row_off[i] = r; tb.tile_off[i] = t;
+            r += m->nbr; t += m->nnzb;
         }
-        tile_off += m->nnzb;
-        row_off += m->nbr;
+        tb.row_off[tb.n] = r; tb.tile_off[tb.n] = t;
+        const int64_t items = (int64_t)r + 1 + (t - tile_off);
+        stack_meta_kernel<<<blocks_for(items, 256), 256, 0, ctx->stream>>>(tb, sentinel, i0 + tb.n == n ? 1 : 0,
+                                                                          out->rowptr + row_off, out->colidx + tile_off);
+        BSP_LAUNCH_CHECK(ctx);
+        if (t > tile_off) {
+            int64_t g = ((t - tile_off) * units + 255) / 256;
+            if (g > (int64_t)ctx->sm_count * 16) g = (int64_t)ctx->sm_count * 16;
+            uint32_t *dst = (uint32_t *)out->vals + (size_t)tile_off * kk;
+            if (vec == 4) stack_vals_kernel<4><<<(unsigned)g, 256, 0, ctx->stream>>>(tb, units, dst);
+            else stack_vals_kernel<1><<<(unsigned)g, 256, 0, ctx->stream>>>(tb, units, dst);
+            BSP_LAUNCH_CHECK(ctx);
+        }
+        tile_off = t;
+        row_off += r;
     }
-    if (n == 0) BSP_CUDA(ctx, cudaMemsetAsync(out->rowptr, 0, sizeof(int32_t), ctx->stream));
     return BSP_OK;
 }
 
-// block rows [row_off, row_off + part->nbr) of `big` -> part (arrays allocated by the caller from tile counts)
-int bsp_split_rows_device(bsp_ctx *ctx, const bsp_mat *big, int32_t row_off, int64_t tile_off, bsp_mat *part)
+// parts[i] (arrays allocated by the caller, nbr / nnzb set) = block rows [row_off[i], row_off[i] + parts[i]->nbr) of
+// `big`, whose tiles start at tile_off[i]; the parts are consecutive in `big`
+int bsp_split_rows_device(bsp_ctx *ctx, const bsp_mat *big, int n, const int32_t *row_off, const int64_t *tile_off,
+                          bsp_mat *const *parts)
 {
-    const size_t tb = (size_t)big->k * big->k * big->esize;
-    split_rowptr_kernel<<<blocks_for((int64_t)part->nbr + 1, 256), 256, 0, ctx->stream>>>(big->rowptr + row_off, part->nbr,
-                                                                                           (int32_t)tile_off, part->rowptr);
-    BSP_LAUNCH_CHECK(ctx);
-    if (part->nnzb) {
-        BSP_CUDA(ctx, cudaMemcpyAsync(part->colidx, big->colidx + tile_off, (size_t)part->nnzb * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-        BSP_CUDA(ctx, cudaMemcpyAsync(part->vals, (const char *)big->vals + (size_t)tile_off * tb, (size_t)part->nnzb * tb,
-                                      cudaMemcpyDeviceToDevice, ctx->stream));
+    const int kk = big->k * big->k * (big->esize / 4);
+    const int vec = (kk % 4 == 0) ? 4 : 1;
+    const int units = kk / vec;
+    for (int i0 = 0; i0 < n; i0 += STACK_MAX) {
+        split_table tb;
+        tb.n = n - i0 < STACK_MAX ? n - i0 : STACK_MAX;
+        for (int i = 0; i < tb.n; i++) {
+            bsp_mat *p = parts[i0 + i];
+            tb.rowptr[i] = p->rowptr; tb.colidx[i] = p->colidx; tb.vals[i] = (uint32_t *)p->vals;
+            tb.row_off[i] = row_off[i0 + i]; tb.tile_off[i] = tile_off[i0 + i];
+        }
+        const bsp_mat *last = parts[i0 + tb.n - 1];
+        tb.row_off[tb.n] = tb.row_off[tb.n - 1] + last->nbr;
+        tb.tile_off[tb.n] = tb.tile_off[tb.n - 1] + last->nnzb;
+        const int64_t tiles = tb.tile_off[tb.n] - tb.tile_off[0];
+        const int64_t items = (int64_t)(tb.row_off[tb.n] - tb.row_off[0]) + tb.n + tiles;
+        split_meta_kernel<<<blocks_for(items, 256), 256, 0, ctx->stream>>>(tb, big->rowptr, big->colidx);
+        BSP_LAUNCH_CHECK(ctx);
+        if (tiles > 0) {
+            int64_t g = (tiles * units + 255) / 256;
+            if (g > (int64_t)ctx->sm_count * 16) g = (int64_t)ctx->sm_count * 16;
+            if (vec == 4) split_vals_kernel<4><<<(unsigned)g, 256, 0, ctx->stream>>>(tb, units, (const uint32_t *)big->vals);
+            else split_vals_kernel<1><<<(unsigned)g, 256, 0, ctx->stream>>>(tb, units, (const uint32_t *)big->vals);
+            BSP_LAUNCH_CHECK(ctx);
+        }
     }
+    return BSP_OK;
+}
+
+// dst_host[i] = src[idx_host[i]]: one small kernel and one copy instead of n copies of 4 bytes
+int bsp_gather_i32_to_host(bsp_ctx *ctx, const int32_t *src, const int32_t *idx_host, int n, int32_t *dst_host)
+{
+    bsp_scratch sc(ctx);
+    int32_t *d_idx = nullptr, *d_out = nullptr;
+    BSP_TRY(sc.alloc(&d_idx, (size_t)n));
+    BSP_TRY(sc.alloc(&d_out, (size_t)n));
+    BSP_CUDA(ctx, cudaMemcpyAsync(d_idx, idx_host, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    gather_i32_kernel<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(src, d_idx, n, d_out);
+    BSP_LAUNCH_CHECK(ctx);
+    BSP_CUDA(ctx, cudaMemcpyAsync(dst_host, d_out, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return BSP_OK;
 }
