@@ -75,6 +75,21 @@ __device__ __forceinline__ int build_row_bitmap(uint32_t *bm, int words, const i
     return nprod;
 }
 
+// Walk the tiles of one B row with the whole warp, four independent index loads per lane and round
+// (a row of a few hundred tiles otherwise costs one exposed L2 round trip per 32 tiles).
+template <typename F>
+__device__ __forceinline__ void for_each_tile_of_row(const int32_t *__restrict__ b_colidx, int b0, int b1, int lane, F f)
+{
+    for (int q0 = b0 + lane; q0 < b1; q0 += 128) {
+        int c[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) c[u] = q0 + 32 * u < b1 ? b_colidx[q0 + 32 * u] : -1;
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (c[u] >= 0) f(q0 + 32 * u, c[u]);
+    }
+}
+
 // Light rows (few tile products) are counted by one warp each; a row whose product count
 // exceeds SYM_HEAVY (R-MAT hubs, dense chain levels) is appended to a list and counted by a
 // whole CTA in sym_count_heavy_kernel, so that one warp never walks 10^5 products alone.
@@ -136,11 +151,8 @@ sym_count_heavy_kernel(const int32_t *__restrict__ heavy_list, const int32_t *__
         for (int p = a0 + warp; p < a1; p += nwarp) { // warps over A entries, lanes over B row j
             const int j = a_colidx[p];
             if (j >= b_nbr) continue;
-            const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
-            for (int q = b0 + lane; q < b1; q += 32) {
-                const int c = b_colidx[q];
-                atomicOr(&bm[c >> 5], 1u << (c & 31));
-            }
+            for_each_tile_of_row(b_colidx, b_rowptr[j], b_rowptr[j + 1], lane,
+                                 [&](int, int c) { atomicOr(&bm[c >> 5], 1u << (c & 31)); });
         }
         __syncthreads();
         int cnt = 0;
@@ -601,11 +613,8 @@ sym_fill_dense_kernel(const int32_t *__restrict__ rowlist, const int32_t *__rest
     for (int e = warp; e < nA; e += nwarp) {
         const int j = a_colidx[a0 + e];
         if (j >= b_nbr) continue;
-        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
-        for (int q = b0 + lane; q < b1; q += 32) {
-            const int c = b_colidx[q];
-            atomicOr(&bm[c >> 5], 1u << (c & 31));
-        }
+        for_each_tile_of_row(b_colidx, b_rowptr[j], b_rowptr[j + 1], lane,
+                             [&](int, int c) { atomicOr(&bm[c >> 5], 1u << (c & 31)); });
     }
     __syncthreads();
     // 2. rank table + sorted colidx of the C row
@@ -632,14 +641,12 @@ sym_fill_dense_kernel(const int32_t *__restrict__ rowlist, const int32_t *__rest
     for (int e = warp; e < nA; e += nwarp) {
         const int j = a_colidx[a0 + e];
         if (j >= b_nbr) continue;
-        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
         const uint32_t ebit = 1u << (e & 31);
         const int ew = e >> 5;
-        for (int q = b0 + lane; q < b1; q += 32) {
-            const int c = b_colidx[q];
+        for_each_tile_of_row(b_colidx, b_rowptr[j], b_rowptr[j + 1], lane, [&](int, int c) {
             const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
             atomicOr(&M[t * W + ew], ebit);
-        }
+        });
     }
     __syncthreads();
     // 4. pairs per tile = popcount of its row of M; scan -> first slot of every tile
@@ -663,11 +670,9 @@ sym_fill_dense_kernel(const int32_t *__restrict__ rowlist, const int32_t *__rest
     for (int e = warp; e < nA; e += nwarp) {
         const int j = a_colidx[a0 + e];
         if (j >= b_nbr) continue;
-        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
         const uint32_t below = (1u << (e & 31)) - 1u;
         const int ew = e >> 5;
-        for (int q = b0 + lane; q < b1; q += 32) {
-            const int c = b_colidx[q];
+        for_each_tile_of_row(b_colidx, b_rowptr[j], b_rowptr[j + 1], lane, [&](int q, int c) {
             const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
             const uint32_t *Mt = M + t * W;
             int r = __popc(Mt[ew] & below);
@@ -675,7 +680,7 @@ sym_fill_dense_kernel(const int32_t *__restrict__ rowlist, const int32_t *__rest
             const int pos = tstart[t] + r;
             const int last = (pos + 1 == tstart[t + 1]) ? (int)0x80000000 : 0;
             pairs[pbase + pos] = make_int2(a0 + e, q | last);
-        }
+        });
     }
 }
 
