@@ -506,7 +506,10 @@ numeric_bigtile_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__re
             const unsigned bsm = wbase + (k & 1) * Cfg::STAGE_BYTES + grp * Cfg::TILE_BYTES;
             const ulonglong2 *arow = reinterpret_cast<const ulonglong2 *>(a_vals + (size_t)cur.x * (K * K) + (size_t)r * K);
             ulonglong2 a0 = arow[0], a1 = arow[1]; // two loads in flight ahead of use
-#pragma unroll
+            // k = 32: 1024 multiply-adds per step; unrolling all of them costs the compiler 200 s (one
+            // 1024-long dependency chain through `flag`) and buys nothing over 128 per loop body
+            constexpr int J2_UNROLL = K >= 32 ? 2 : K / 2;
+#pragma unroll J2_UNROLL
             for (int j2 = 0; j2 < K / 2; j2++) {
                 const ulonglong2 av = a0;
                 a0 = a1;
@@ -654,9 +657,11 @@ int launch_rows(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
                 const int32_t *c_rowptr, uint64_t *c_vals)
 {
     const NumericTuning tn = numeric_tuning();
+#ifdef BSP_TUNING_VARIANTS // three more instantiations per tile size: +3 minutes of build time, measured no faster
     if (tn.stages == 3 && tn.warps == 4) return launch_rows_cfg<K, 3, 4>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
     if (tn.stages == 2 && tn.warps == 8) return launch_rows_cfg<K, 2, 8>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
     if (tn.stages == 3 && tn.warps == 8) return launch_rows_cfg<K, 3, 8>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
+#endif
     return launch_rows_cfg<K, 2, 4>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
 }
 
