@@ -14,7 +14,8 @@
 // every sub-chain is reduced by the pairwise tree, the P partial products are reduced by the
 // same tree (cu:569-571), and all-zero tiles are dropped from the final product (cu:577-592).
 // Sub-chain r runs on CUDA device r mod D on its own host thread; partial products move
-// device-to-device into device 0, which does the merge.  Default P = 1, D = all visible.
+// device-to-device into device 0, and every large product of the merge is sharded by block rows over
+// the D devices (same tree, same bits).  Default P = 1, D = all visible.
 //
 // Additions without a counterpart in the reference (off by default, the default run is the
 // reference's): --binary reads <folder>/matrixI.bin where it exists (else the text file) and
@@ -86,6 +87,119 @@ void run_rank(Rank *r, const std::string &folder, int k, bool binary)
     r->rc = bsp_chain(r->ctx, r->mats.data(), n, &r->partial, nullptr, log.data(), log.size(), r->start);
     if (r->rc) { r->err = bsp_last_error(r->ctx); return; }
     r->log = log.data();
+}
+
+// One product of the merge, sharded over the devices: device d multiplies the block rows
+// [bounds[d], bounds[d+1]) of L (balanced by tiles per row) by R.  Rows are independent and every
+// output element keeps its accumulation order, so the concatenated panels equal L*R bit for bit.
+// devs[0] is the context that holds L and R and receives the product.  Each context is used by one
+// thread at a time: the copies to and from the other devices are made by the calling thread, only the
+// panel products run side by side.
+int sharded_product(const std::vector<bsp_ctx *> &devs, const bsp_mat *L, const bsp_mat *R, bsp_mat **out, std::string *err)
+{
+    bsp_ctx *root = devs[0];
+    const int D = (int)devs.size();
+    int64_t nl = 0, nr = 0;
+    bsp_mat_info(L, nullptr, nullptr, nullptr, &nl);
+    bsp_mat_info(R, nullptr, nullptr, nullptr, &nr);
+    int64_t shard_min = 200000; // tiles of L and R together; BSP_A4_SHARD_MIN lowers it for tests
+    if (const char *e = getenv("BSP_A4_SHARD_MIN")) shard_min = atoll(e);
+    if (D == 1 || nl + nr < shard_min) { // small product: moving it would cost more than it saves
+        int rc = bsp_spgemm(root, L, R, out, nullptr);
+        if (rc) *err = bsp_last_error(root);
+        return rc;
+    }
+    int32_t nbr = 0;
+    bsp_mat_device_view(L, &nbr, nullptr, nullptr, nullptr, nullptr);
+    std::vector<int32_t> brow((size_t)nl);
+    int rc = bsp_mat_to_coo(root, L, brow.data(), nullptr, nullptr);
+    if (rc) { *err = bsp_last_error(root); return rc; }
+    std::vector<int32_t> bounds((size_t)D + 1, nbr);
+    bounds[0] = 0;
+    for (int d = 1; d < D; d++) { // first row whose first tile is at or beyond d/D of all tiles (brow is sorted)
+        const int64_t want = nl * d / D;
+        bounds[(size_t)d] = want < nl ? brow[(size_t)want] : nbr;
+        if (bounds[(size_t)d] < bounds[(size_t)d - 1]) bounds[(size_t)d] = bounds[(size_t)d - 1];
+    }
+    std::vector<bsp_mat *> Ld((size_t)D, nullptr), Rd((size_t)D, nullptr), panel((size_t)D, nullptr), home((size_t)D, nullptr);
+    std::vector<int> prc((size_t)D, 0);
+    for (int d = 1; d < D && !rc; d++) {
+        rc = bsp_mat_copy_to_ctx(root, L, devs[(size_t)d], &Ld[(size_t)d]);
+        if (!rc) rc = bsp_mat_copy_to_ctx(root, R, devs[(size_t)d], &Rd[(size_t)d]);
+        if (rc) *err = bsp_last_error(devs[(size_t)d]);
+    }
+    if (!rc) {
+        std::vector<std::thread> th;
+        for (int d = 0; d < D; d++)
+            th.emplace_back([&, d]() {
+                prc[(size_t)d] = bsp_spgemm_panel(devs[(size_t)d], d ? Ld[(size_t)d] : L, d ? Rd[(size_t)d] : R, bounds[(size_t)d],
+                                                  bounds[(size_t)d + 1], &panel[(size_t)d], nullptr);
+            });
+        for (auto &t : th) t.join();
+        for (int d = 0; d < D && !rc; d++)
+            if (prc[(size_t)d]) { rc = prc[(size_t)d]; *err = bsp_last_error(devs[(size_t)d]); }
+    }
+    home[0] = panel[0];
+    for (int d = 1; d < D && !rc; d++) {
+        rc = bsp_mat_copy_to_ctx(devs[(size_t)d], panel[(size_t)d], root, &home[(size_t)d]);
+        if (rc) *err = bsp_last_error(root);
+    }
+    if (!rc) {
+        rc = bsp_mat_concat_panels(root, home.data(), D, out);
+        if (rc) *err = bsp_last_error(root);
+    }
+    for (int d = 0; d < D; d++) {
+        bsp_mat_free(devs[(size_t)d], Ld[(size_t)d]);
+        bsp_mat_free(devs[(size_t)d], Rd[(size_t)d]);
+        bsp_mat_free(devs[(size_t)d], panel[(size_t)d]);
+        if (d) bsp_mat_free(root, home[(size_t)d]);
+    }
+    return rc;
+}
+
+// The reference's rank 0 reduces the P partial products with helper2 (cu:569-571): adjacent pairs,
+// odd tail carried (cu:297-320), one "multiplying a b" line per product (cu:301).  Same tree here,
+// every product through sharded_product.  `parts` are owned by the caller.
+int merge_partials(const std::vector<bsp_ctx *> &devs, const std::vector<bsp_mat *> &parts, bsp_mat **out, std::string *log,
+                   std::string *err)
+{
+    bsp_ctx *root = devs[0];
+    std::vector<bsp_mat *> cur(parts);
+    std::vector<char> owned(parts.size(), 0);
+    int rc = 0;
+    while (cur.size() > 1 && !rc) {
+        const size_t len = cur.size();
+        std::vector<bsp_mat *> nxt;
+        std::vector<char> nxt_owned;
+        for (size_t i = 0; i + 1 < len; i += 2) *log += "multiplying " + std::to_string(i) + " " + std::to_string(i + 1) + "\n";
+        for (size_t i = 0; i + 1 < len && !rc; i += 2) {
+            bsp_mat *c = nullptr;
+            rc = sharded_product(devs, cur[i], cur[i + 1], &c, err);
+            if (rc) { bsp_mat_free(root, c); break; }
+            nxt.push_back(c);
+            nxt_owned.push_back(1);
+            if (owned[i]) bsp_mat_free(root, cur[i]);
+            if (owned[i + 1]) bsp_mat_free(root, cur[i + 1]);
+            cur[i] = cur[i + 1] = nullptr;
+        }
+        if (!rc && (len & 1)) {
+            nxt.push_back(cur[len - 1]);
+            nxt_owned.push_back(owned[len - 1]);
+            cur[len - 1] = nullptr;
+        }
+        if (rc) {
+            for (size_t i = 0; i < nxt.size(); i++) if (nxt_owned[i]) bsp_mat_free(root, nxt[i]);
+            for (size_t i = 0; i < cur.size(); i++) if (cur[i] && owned[i]) bsp_mat_free(root, cur[i]);
+            return rc;
+        }
+        cur.swap(nxt);
+        owned.swap(nxt_owned);
+    }
+    if (owned[0]) { *out = cur[0]; return 0; }
+    // a single partial product: helper2 leaves it as it is; hand back a copy the caller may free
+    rc = bsp_mat_copy_to_ctx(root, cur[0], root, out);
+    if (rc) *err = bsp_last_error(root);
+    return rc;
 }
 
 } // namespace
@@ -186,10 +300,16 @@ int main(int argc, char **argv)
             }
             if (!rc) {
                 bsp_ctx_sync(probe);
-                std::vector<char> log(parts.size() * 64 + 64);
-                int e = bsp_chain(probe, parts.data(), (int)parts.size(), &result, nullptr, log.data(), log.size(), 0);
-                if (e) { fprintf(stderr, "a4: merge: %s\n", bsp_last_error(probe)); rc = 3; }
-                else fputs(log.data(), stdout);
+                // one context per device for the sharded merge: device 0 = probe, device d = the context of
+                // the first sub-chain that ran there (its thread has finished)
+                std::vector<bsp_ctx *> devs{probe};
+                for (int d = 1; d < D; d++)
+                    for (auto &r : ranks)
+                        if (r.device == d) { devs.push_back(r.ctx); break; }
+                std::string log, err;
+                int e = merge_partials(devs, parts, &result, &log, &err);
+                if (e) { fprintf(stderr, "a4: merge: %s\n", err.c_str()); rc = 3; }
+                else fputs(log.c_str(), stdout);
             }
             for (auto *m : parts) bsp_mat_free(probe, m);
         }

@@ -28,12 +28,24 @@ def test_a4_two_devices_matches_two_rank_reference_tree():
     exe = os.path.join(os.path.dirname(bspgemm.__file__), "a4")
     with tempfile.TemporaryDirectory() as d:
         orc.write_folder(os.path.join(d, "in"), mats, k)
-        p = subprocess.run([exe, os.path.join(d, "in"), "--ranks", "2", "--devices", "2"], cwd=d,
-                           stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=300)
-        assert p.returncode == 0, p.stderr.decode()
         want = orc.chain(mats, ranks=2)[0].prune_zero()
         want.write(os.path.join(d, "want"))
-        assert open(os.path.join(d, "matrix"), "rb").read() == open(os.path.join(d, "want"), "rb").read()
+        logs = []
+        # second run: every product of the merge sharded by block rows over the two devices
+        for env in (os.environ, dict(os.environ, BSP_A4_SHARD_MIN="1")):
+            p = subprocess.run([exe, os.path.join(d, "in"), "--ranks", "2", "--devices", "2"], cwd=d, env=env,
+                               stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=300)
+            assert p.returncode == 0, p.stderr.decode()
+            assert open(os.path.join(d, "matrix"), "rb").read() == open(os.path.join(d, "want"), "rb").read()
+            logs.append([ln for ln in p.stdout.decode().splitlines() if ln.startswith("multiplying")])
+            os.remove(os.path.join(d, "matrix"))
+        assert logs[0] == logs[1] and logs[0][-1] == "multiplying 0 1"
+        # four ranks on two devices: two merge levels, the partial of rank 3 is a longer sub-chain
+        p = subprocess.run([exe, os.path.join(d, "in"), "--ranks", "4", "--devices", "2"], cwd=d,
+                           env=dict(os.environ, BSP_A4_SHARD_MIN="1"), stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=300)
+        assert p.returncode == 0, p.stderr.decode()
+        orc.chain(mats, ranks=4)[0].prune_zero().write(os.path.join(d, "want4"))
+        assert open(os.path.join(d, "matrix"), "rb").read() == open(os.path.join(d, "want4"), "rb").read()
 
 
 NCCL_WORKER = r'''

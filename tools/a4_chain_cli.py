@@ -2,7 +2,8 @@
 """End-to-end time of the drop-in CLI on bench.py's chain workload (64 banded matrices, n=16384, k=4):
 `a4 <folder>` reading the reference's text files and writing ./matrix, and `a4 --binary --checksum`
 on the same matrices as BSPMAT01 files.  Wall clock of the whole process (CUDA context creation
-included) next to a4's own `time taken` line.  Prints one JSON line."""
+included) next to a4's own `time taken` line.  Extra arguments (e.g. --ranks 2 --devices 2) are passed
+to a4.  Prints one JSON line."""
 import json
 import os
 import re
@@ -39,7 +40,7 @@ def main():
             best = None
             for _ in range(2):
                 t0 = time.perf_counter()
-                p = subprocess.run([exe, folder] + flags, cwd=dd, capture_output=True, text=True)
+                p = subprocess.run([exe, folder] + flags + sys.argv[1:], cwd=dd, capture_output=True, text=True)
                 wall = time.perf_counter() - t0
                 assert p.returncode == 0, p.stderr
                 own = float(re.search(r"time taken ([0-9.eE+-]+) seconds", p.stdout).group(1))
@@ -51,6 +52,7 @@ def main():
                     if m:
                         best["checksum"] = m.group(1)
             out[name] = best
+    out["a4_args"] = sys.argv[1:]
     print(json.dumps(out))
 
 
