@@ -498,3 +498,89 @@ def test_banded_chain_bit_matrix_fill(monkeypatch):
     monkeypatch.setenv("BSP_SYM_NO_DENSE", "1")
     with bspgemm.Context(0) as c2:
         assert c2.helper2([c2.matrix_from_coo(*m) for m in mats]).checksum() == sums
+
+
+def _rmat(scale, k, seed, kind):
+    br, bc = bsp_gen.rmat_pattern(scale, 16, seed)
+    G = 1 << scale
+    return G * k, G * k, k, br, bc, bsp_gen.values(seed, br.size * k * k, kind).reshape(-1, k, k)
+
+
+def test_rmat_small_against_oracle_and_panels(ctx):
+    """BASELINE.json configs[3] at test size (R-MAT scale 9, edge factor 16: hub rows with thousands
+    of tile products next to rows with a handful): whole product against the oracle, and 8 block-row
+    panels balanced by tile products, concatenated, against the whole product."""
+    k, scale = 8, 9
+    G = 1 << scale
+    a, b = _rmat(scale, k, 11, "edgy"), _rmat(scale, k, 12, "u64")
+    want, nprod = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b), threads=8)
+    A, B = dev(ctx, a), dev(ctx, b)
+    st = bspgemm.Stats()
+    full = ctx.helper(A, B, stats=st)
+    assert_same(full, want)
+    assert st.nprod == nprod
+    rowlen_b = np.bincount(b[3], minlength=G)
+    work = np.bincount(a[3], weights=rowlen_b[a[4]], minlength=G)
+    bounds = bsp_dist.balanced_panels(work, 8)
+    parts = [ctx.helper(A, B, panel=(bounds[i], bounds[i + 1])) for i in range(8)]
+    assert ctx.concat_panels(parts).checksum() == full.checksum()
+
+
+def test_rmat_full_size_panels_and_sampled_tiles(ctx):
+    """configs[3] in full (scale 15, n=262144, k=8, 1.47e8 tile products, 5.8e7 output tiles): the
+    product computed whole equals the 8 balanced panels concatenated (content checksum), the hub rows
+    take the multi-launch fill, and sampled output tiles -- the longest pair lists among them -- equal
+    a Python-int evaluation of the reference arithmetic."""
+    k, scale = 8, 15
+    G = 1 << scale
+    a, b = _rmat(scale, k, 11, "u64"), _rmat(scale, k, 12, "u64")
+    A, B = dev(ctx, a), dev(ctx, b)
+    st = bspgemm.Stats()
+    full = ctx.helper(A, B, stats=st)
+    rowlen_b = np.bincount(b[3], minlength=G)
+    work = np.bincount(a[3], weights=rowlen_b[a[4]], minlength=G)
+    assert st.nprod == int(work.sum()) and work.max() > (1 << 18)   # at least one row above hv_min
+    whole = full.checksum()
+    bounds = bsp_dist.balanced_panels(work, 8)
+    parts = [ctx.helper(A, B, panel=(bounds[i], bounds[i + 1])) for i in range(8)]
+    cat = ctx.concat_panels(parts)
+    assert cat.nnzb == full.nnzb and cat.checksum() == whole
+    del parts, cat
+    # tiles of the heaviest row and of random rows; duplicates of the generator were resolved on ingest
+    # (last wins), so take the operands back from the device
+    abr, abc, av = A.to_coo()
+    bbr, bbc, bv = B.to_coo()
+    a_key = abr.astype(np.int64) * G + abc
+    b_key = bbr.astype(np.int64) * G + bbc
+    nbr, nbc, rp_ptr, ci_ptr, _ = full.device_view()
+    import torch
+    rowptr = torch.empty(nbr + 1, dtype=torch.int32, device="cuda:0")
+    colidx = torch.empty(full.nnzb, dtype=torch.int32, device="cuda:0")
+    vals = torch.empty(full.nnzb * k * k, dtype=torch.int64, device="cuda:0")
+    full.export_device(rowptr.data_ptr(), colidx.data_ptr(), vals.data_ptr())
+    rp = rowptr.cpu().numpy()
+    hub = int(np.argmax(work))
+    rng = np.random.default_rng(3)
+    picks = [(hub, int(x)) for x in rng.integers(rp[hub], rp[hub + 1], 6)]
+    picks += [(int(np.searchsorted(rp, t, side="right") - 1), int(t)) for t in rng.integers(0, full.nnzb, 10)]
+    for i, t in picks:
+        c = int(colidx[t].item())
+        got = vals[t * k * k:(t + 1) * k * k].cpu().numpy().view(np.uint64).reshape(k, k)
+        js = abc[np.searchsorted(abr, i):np.searchsorted(abr, i + 1)]
+        acc = [[0] * k for _ in range(k)]
+        for j in js:
+            q = np.searchsorted(b_key, int(j) * G + c)
+            if q < b_key.size and b_key[q] == int(j) * G + c:
+                At, Bt = av[np.searchsorted(a_key, i * G + int(j))], bv[q]
+                for r in range(k):
+                    for cc in range(k):
+                        s = acc[r][cc]
+                        for x in range(k):
+                            p = (int(At[r, x]) * int(Bt[x, cc])) & MAXV
+                            p = 0 if p == MAXV else p
+                            s = (s + p) & MAXV
+                            s = 0 if s == MAXV else s
+                        acc[r][cc] = s
+        assert np.array_equal(np.array(acc, dtype=np.uint64), got), (i, c)
+    del rowptr, colidx, vals
+    torch.cuda.empty_cache()
