@@ -993,7 +993,7 @@ __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowp
     if (nA > acap) cls = 4;                                  // A row too long for the shared-memory entry table
     if (tiny_ok && P <= TINY_P && nA <= TINY_A) cls = 0;     // warp-per-row sort
     if (cls == 4 && P > hv_min) cls = 5;                     // spread over the whole GPU
-    if (dense_ok && cls != 0 && P >= DENSE_MIN_RATIO * T) {  // many pairs per tile: bit-matrix placement
+    if (dense_ok && cls != 0 && P >= dense_ok * T) {   // dense_ok = minimum tile products per output tile  // many pairs per tile: bit-matrix placement
         const int mw = T <= DENSE_M1 ? dense_need_words(T, nA) : DENSE_M1 + 1;
         if (mw <= DENSE_M0) cls = 6;
         else if (mw <= DENSE_M1) cls = 7;
@@ -1118,7 +1118,11 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     // (measured: chain top product, 66 k products per row: 3.3 ms against 38 ms).  BSP_HV_MIN_P is a test hook.
     int hv_min = 1 << 18;
     if (const char *e = getenv("BSP_HV_MIN_P")) { const int v = atoi(e); if (v > 0) hv_min = v; }
-    const int dense_ok = getenv("BSP_SYM_NO_DENSE") ? 0 : 1; // comparison hook: rows keep their capacity class
+    // 0 = rows keep their capacity class (BSP_SYM_NO_DENSE, a comparison hook), else the minimum number of tile
+    // products per output tile for the bit-matrix fill (BSP_SYM_DENSE_RATIO overrides the default)
+    int dense_ok = getenv("BSP_SYM_NO_DENSE") ? 0 : DENSE_MIN_RATIO;
+    if (dense_ok)
+        if (const char *e = getenv("BSP_SYM_DENSE_RATIO")) { const int v = atoi(e); if (v > 0) dense_ok = v; }
     // the tiny-row kernel packs the block column into 27 bits; BSP_SYM_CAPS (a test hook) also switches it off
     const int tiny_ok = (B->nbc < (1 << 27) && !getenv("BSP_SYM_CAPS")) ? 1 : 0;
     for (int c = 0; c < 3; c++) {
