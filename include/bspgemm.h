@@ -85,7 +85,7 @@ int bsp_mat_is_f32(const bsp_mat *m);
  * 2 = tensor cores (k = 32 or 64) */
 int bsp_ctx_set_f32_path(bsp_ctx *ctx, int path);
 
-/* Same, from DEVICE memory (arrays are copied, not adopted). */
+/* Same, from DEVICE memory (arrays are copied, not adopted: the copies are complete on return). */
 int bsp_mat_from_device_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int64_t nnzb,
                             const int32_t *d_brow, const int32_t *d_bcol, const uint64_t *d_vals,
                             bsp_mat **out);
@@ -116,10 +116,15 @@ int bsp_mat_export_device(bsp_ctx *ctx, const bsp_mat *m, int32_t *d_rowptr, int
 int bsp_mat_copy_to_ctx(bsp_ctx *src_ctx, const bsp_mat *m, bsp_ctx *dst_ctx, bsp_mat **out);
 
 /* Build a matrix from a device CSR-of-blocks view (arrays are copied).  The receiving side
- * of the partial-product exchange that replaces MPI_Recv + map rebuild (cu:513-551). */
+ * of the partial-product exchange that replaces MPI_Recv + map rebuild (cu:513-551).  The copies
+ * are complete on return. */
 int bsp_mat_from_device_bcsr(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows,
                              int32_t nbcols, int64_t nnzb, const int32_t *d_rowptr,
                              const int32_t *d_colidx, const uint64_t *d_vals, bsp_mat **out);
+/* Same for float32 tiles (extension, see bsp_mat_from_coo_f32; no reference counterpart). */
+int bsp_mat_from_device_bcsr_f32(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows,
+                                 int32_t nbcols, int64_t nnzb, const int32_t *d_rowptr,
+                                 const int32_t *d_colidx, const float *d_vals, bsp_mat **out);
 
 void bsp_mat_free(bsp_ctx *ctx, bsp_mat *m);
 

@@ -59,6 +59,7 @@ _SIGNATURES = {
     "bsp_mat_export_device": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "bsp_mat_copy_to_ctx": (C.c_int, [_VP, _VP, _VP, C.POINTER(_VP)]),
     "bsp_mat_from_device_bcsr": (C.c_int, [_VP, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP, C.POINTER(_VP)]),
+    "bsp_mat_from_device_bcsr_f32": (C.c_int, [_VP, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64, _VP, _VP, _VP, C.POINTER(_VP)]),
     "bsp_mat_free": (None, [_VP, _VP]),
     "bsp_spgemm": (C.c_int, [_VP, _VP, _VP, C.POINTER(_VP), C.POINTER(Stats)]),
     "bsp_spgemm_panel": (C.c_int, [_VP, _VP, _VP, C.c_int32, C.c_int32, C.POINTER(_VP), C.POINTER(Stats)]),

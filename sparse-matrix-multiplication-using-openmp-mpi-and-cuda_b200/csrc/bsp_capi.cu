@@ -78,15 +78,22 @@ int spgemm_impl(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_lo
     c->rowptr = sym.c_rowptr; // from here on bsp_mat_free(c) releases the pattern arrays
     c->colidx = sym.c_colidx;
     c->nnzb = sym.nnzb_c;
-    cudaEventRecord(ctx->ev[1], ctx->stream);
-    rc = bsp_alloc(ctx, (char **)&c->vals, (size_t)sym.nnzb_c * A->k * A->k * A->esize);
+    rc = BSP_OK;
+    if (cudaEventRecord(ctx->ev[1], ctx->stream) != cudaSuccess) {
+        snprintf(ctx->err, sizeof(ctx->err), "bsp_spgemm: cudaEventRecord failed: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = BSP_ERR_CUDA;
+    }
+    if (rc == BSP_OK) rc = bsp_alloc(ctx, (char **)&c->vals, (size_t)sym.nnzb_c * A->k * A->k * A->esize);
     bsp_trace_mark(ctx, "alloc_c");
     if (rc == BSP_OK) {
         if (A->esize == 8) rc = bsp_numeric(ctx, A, B, &sym, c->vals, &st.exact_refolds, &st.numeric_path);
         else rc = bsp_numeric_f32(ctx, A, B, &sym, (float *)c->vals, &st.numeric_path);
     }
     bsp_trace_mark(ctx, "numeric");
-    cudaEventRecord(ctx->ev[2], ctx->stream);
+    if (rc == BSP_OK && cudaEventRecord(ctx->ev[2], ctx->stream) != cudaSuccess) {
+        snprintf(ctx->err, sizeof(ctx->err), "bsp_spgemm: cudaEventRecord failed: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = BSP_ERR_CUDA;
+    }
     bsp_release(ctx, sym.pair_ptr);
     bsp_release(ctx, sym.pairs);
     if (rc != BSP_OK) { bsp_mat_free(ctx, c); return rc; }
@@ -302,7 +309,9 @@ int bsp_mat_from_device_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k,
             if (hc[i] > max_col) max_col = hc[i];
         }
     }
-    return bsp_ingest_coo(ctx, rows, cols, k, 8, nnzb, d_brow, d_bcol, d_vals, max_row, max_col, out);
+    BSP_TRY(bsp_ingest_coo(ctx, rows, cols, k, 8, nnzb, d_brow, d_bcol, d_vals, max_row, max_col, out));
+    BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // "copied, not adopted": the caller may reuse its arrays on return
+    return BSP_OK;
 }
 
 static int from_coo_impl(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t esize, int64_t nnzb,
@@ -451,23 +460,45 @@ int bsp_mat_copy_to_ctx(bsp_ctx *src_ctx, const bsp_mat *m, bsp_ctx *dst_ctx, bs
     return BSP_OK;
 }
 
-int bsp_mat_from_device_bcsr(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows, int32_t nbcols,
-                             int64_t nnzb, const int32_t *d_rowptr, const int32_t *d_colidx, const uint64_t *d_vals,
-                             bsp_mat **out)
+static int from_device_bcsr_impl(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t esize, int32_t nbrows,
+                                 int32_t nbcols, int64_t nnzb, const int32_t *d_rowptr, const int32_t *d_colidx,
+                                 const void *d_vals, bsp_mat **out)
 {
     if (!ctx || !out) return BSP_ERR_ARG;
     *out = nullptr;
-    if (k < 1 || nbrows < 0 || nbcols < 0 || nnzb < 0 || !d_rowptr)
+    if (k < 1 || nbrows < 0 || nbcols < 0 || nnzb < 0 || !d_rowptr || (nnzb > 0 && (!d_colidx || !d_vals)))
         BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_from_device_bcsr: bad arguments");
     BSP_CUDA(ctx, cudaSetDevice(ctx->device));
     bsp_mat tmp;
     tmp.rows = rows; tmp.cols = cols; tmp.k = k; tmp.nbr = nbrows; tmp.nbc = nbcols; tmp.nnzb = nnzb;
     tmp.rowptr = const_cast<int32_t *>(d_rowptr);
     tmp.colidx = const_cast<int32_t *>(d_colidx);
-    tmp.vals = const_cast<uint64_t *>(d_vals);
+    tmp.vals = reinterpret_cast<uint64_t *>(const_cast<void *>(d_vals));
     tmp.device = ctx->device;
-    tmp.esize = 8;
-    return clone_mat(ctx, &tmp, out);
+    tmp.esize = esize;
+    int rc = clone_mat(ctx, &tmp, out);
+    // "copied, not adopted": the copies are complete when the call returns, so the caller may free or
+    // overwrite its arrays on any stream
+    if (rc == BSP_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+        snprintf(ctx->err, sizeof(ctx->err), "bsp_mat_from_device_bcsr: copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = BSP_ERR_CUDA;
+    }
+    if (rc != BSP_OK) { bsp_mat_free(ctx, *out); *out = nullptr; }
+    return rc;
+}
+
+int bsp_mat_from_device_bcsr(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows, int32_t nbcols,
+                             int64_t nnzb, const int32_t *d_rowptr, const int32_t *d_colidx, const uint64_t *d_vals,
+                             bsp_mat **out)
+{
+    return from_device_bcsr_impl(ctx, rows, cols, k, 8, nbrows, nbcols, nnzb, d_rowptr, d_colidx, d_vals, out);
+}
+
+int bsp_mat_from_device_bcsr_f32(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t nbrows, int32_t nbcols,
+                                 int64_t nnzb, const int32_t *d_rowptr, const int32_t *d_colidx, const float *d_vals,
+                                 bsp_mat **out)
+{
+    return from_device_bcsr_impl(ctx, rows, cols, k, 4, nbrows, nbcols, nnzb, d_rowptr, d_colidx, d_vals, out);
 }
 
 void bsp_mat_free(bsp_ctx *ctx, bsp_mat *m)
@@ -663,6 +694,7 @@ int bsp_multiply_host(bsp_ctx *ctx, int32_t k, int32_t rows_a, int32_t cols_a, i
             lo = hi;
             if (rc != BSP_OK) break;
             accumulate(&tot, st);
+            tot.nnzb_b = st.nnzb_b; // B is the same in every panel: count it once
             bsp_mat *P = panels[p];
             if (done + P->nnzb > cap_c) {
                 snprintf(ctx->err, sizeof(ctx->err), "bsp_multiply_host: result has more than %lld tiles (capacity)", (long long)cap_c);
@@ -674,11 +706,20 @@ int bsp_multiply_host(bsp_ctx *ctx, int32_t k, int32_t rows_a, int32_t cols_a, i
                 if (rc == BSP_OK) rc = bsp_expand_rows(ctx, P, d_brow[p]);
                 if (rc != BSP_OK) break;
                 // copy stream waits for this panel, then downloads it while the next panel is computed
-                cudaEventRecord(ctx->ev[3], ctx->stream);
-                cudaStreamWaitEvent(ctx->copy_stream, ctx->ev[3], 0);
-                if (brow_c) cudaMemcpyAsync(brow_c + done, d_brow[p], (size_t)P->nnzb * 4, cudaMemcpyDeviceToHost, ctx->copy_stream);
-                if (bcol_c) cudaMemcpyAsync(bcol_c + done, P->colidx, (size_t)P->nnzb * 4, cudaMemcpyDeviceToHost, ctx->copy_stream);
-                if (vals_c) cudaMemcpyAsync((char *)vals_c + (size_t)done * tb, P->vals, (size_t)P->nnzb * tb, cudaMemcpyDeviceToHost, ctx->copy_stream);
+                cudaError_t ce = cudaEventRecord(ctx->ev[3], ctx->stream);
+                if (ce == cudaSuccess) ce = cudaStreamWaitEvent(ctx->copy_stream, ctx->ev[3], 0);
+                if (ce == cudaSuccess && brow_c)
+                    ce = cudaMemcpyAsync(brow_c + done, d_brow[p], (size_t)P->nnzb * 4, cudaMemcpyDeviceToHost, ctx->copy_stream);
+                if (ce == cudaSuccess && bcol_c)
+                    ce = cudaMemcpyAsync(bcol_c + done, P->colidx, (size_t)P->nnzb * 4, cudaMemcpyDeviceToHost, ctx->copy_stream);
+                if (ce == cudaSuccess && vals_c)
+                    ce = cudaMemcpyAsync((char *)vals_c + (size_t)done * tb, P->vals, (size_t)P->nnzb * tb, cudaMemcpyDeviceToHost, ctx->copy_stream);
+                if (ce != cudaSuccess) {
+                    snprintf(ctx->err, sizeof(ctx->err), "bsp_multiply_host: queuing the download of panel %d failed: %s", p, cudaGetErrorString(ce));
+                    cudaGetLastError();
+                    rc = BSP_ERR_CUDA;
+                    break;
+                }
                 done += P->nnzb;
             }
         }
@@ -696,7 +737,7 @@ int bsp_multiply_host(bsp_ctx *ctx, int32_t k, int32_t rows_a, int32_t cols_a, i
                 t_panels - t_start, t_copied - t_start);
     if (rc == BSP_OK) {
         *nnzb_c = done;
-        tot.nnzb_a = nnzb_a; tot.nnzb_b = B ? tot.nnzb_b / NP : 0;
+        tot.nnzb_a = nnzb_a;
         if (stats) *stats = tot;
     }
     return rc;

@@ -10,6 +10,8 @@
 //            per-tile predicate, exclusive scan, compaction of colidx / vals / rowptr.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <new>
+
 #include "bsp_internal.h"
 
 namespace {
@@ -168,7 +170,9 @@ int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t 
                    const int32_t *d_brow, const int32_t *d_bcol, const void *d_vals, int32_t max_row, int32_t max_col,
                    bsp_mat **out)
 {
-    bsp_mat *m = new bsp_mat();
+    *out = nullptr;
+    bsp_mat *m = new (std::nothrow) bsp_mat();
+    if (!m) BSP_FAIL(ctx, BSP_ERR_NOMEM, "host allocation failed");
     m->rows = rows; m->cols = cols; m->k = k; m->device = ctx->device; m->esize = esize;
     m->nbr = nnzb > 0 ? max_row + 1 : 0;
     m->nbc = nnzb > 0 ? max_col + 1 : 0;

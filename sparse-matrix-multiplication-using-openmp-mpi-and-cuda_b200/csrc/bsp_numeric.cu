@@ -244,6 +244,8 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
                     uint64_t *__restrict__ c_vals, unsigned long long *__restrict__ refold_count)
 {
     using Cfg = RowsCfg<K>;
+    // the A tiles have ONE buffer (rows go to registers at step start): a deeper prologue would overwrite them
+    static_assert(STAGES == 2, "numeric_rows_kernel: A tiles are single-buffered, only two B stages are valid");
     constexpr int TPT = Cfg::TPT, RPT = Cfg::RPT;
     constexpr int NCOPY = 2 * Cfg::GROUPS * Cfg::IPT / Cfg::TPI; // warp-wide cp.async instructions per step
     extern __shared__ __align__(16) unsigned char smem[];
@@ -556,7 +558,6 @@ NumericTuning numeric_tuning()
     NumericTuning tn = {96, 1 << 20, 2, 4, false}; // panels off by default: measured no gain on cfg2 (see profiles/)
     if (const char *e = getenv("BSP_NUM_Q")) { int v = atoi(e); if (v >= 1) { tn.Q = v; tn.q_forced = true; } }
     if (const char *e = getenv("BSP_NUM_PANEL_MB")) { int v = atoi(e); if (v >= 1) tn.panel_mb = v; }
-    if (const char *e = getenv("BSP_NUM_STAGES")) { int v = atoi(e); if (v == 2 || v == 3) tn.stages = v; }
     if (const char *e = getenv("BSP_NUM_WARPS")) { int v = atoi(e); if (v == 4 || v == 8) tn.warps = v; }
     return tn;
 }
@@ -657,10 +658,8 @@ int launch_rows(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
                 const int32_t *c_rowptr, uint64_t *c_vals)
 {
     const NumericTuning tn = numeric_tuning();
-#ifdef BSP_TUNING_VARIANTS // three more instantiations per tile size: +3 minutes of build time, measured no faster
-    if (tn.stages == 3 && tn.warps == 4) return launch_rows_cfg<K, 3, 4>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
-    if (tn.stages == 2 && tn.warps == 8) return launch_rows_cfg<K, 2, 8>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
-    if (tn.stages == 3 && tn.warps == 8) return launch_rows_cfg<K, 3, 8>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
+#ifdef BSP_TUNING_VARIANTS // one more instantiation per tile size, measured no faster
+    if (tn.warps == 8) return launch_rows_cfg<K, 2, 8>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
 #endif
     return launch_rows_cfg<K, 2, 4>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
 }

@@ -99,7 +99,8 @@ __global__ void __launch_bounds__(SYM_THREADS)
 sym_count_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t *__restrict__ a_colidx, int b_nbr,
                  const int32_t *__restrict__ b_rowptr, const int32_t *__restrict__ b_colidx, int words, int row_lo,
                  int row_hi, int32_t *__restrict__ row_cnt, int32_t *__restrict__ row_prod,
-                 int32_t *__restrict__ heavy_list, int32_t *__restrict__ heavy_count)
+                 int32_t *__restrict__ heavy_list, int32_t *__restrict__ heavy_count,
+                 int32_t *__restrict__ overflow_flag)
 {
     extern __shared__ uint32_t smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -107,13 +108,21 @@ sym_count_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t 
     for (int row = blockIdx.x * SYM_WARPS + warp; row < a_nbr; row += gridDim.x * SYM_WARPS) {
         int cnt = 0, nprod = 0;
         if (row >= row_lo && row < row_hi && a_rowptr[row + 1] > a_rowptr[row]) {
-            // tile products of the row: lanes over the A entries
+            // tile products of the row: lanes over the A entries.  Summed in 64 bits: the per-row counts
+            // are kept as int32, a row beyond 2^31-1 products raises the flag (BSP_ERR_LIMIT on the host)
             const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
+            long long np64 = 0;
             for (int p = a0 + lane; p < a1; p += 32) {
                 const int j = a_colidx[p];
-                if (j < b_nbr) nprod += b_rowptr[j + 1] - b_rowptr[j];
+                if (j < b_nbr) np64 += b_rowptr[j + 1] - b_rowptr[j];
             }
-            nprod = warp_sum(nprod);
+#pragma unroll
+            for (int d = 16; d; d >>= 1) np64 += __shfl_xor_sync(0xffffffffu, np64, d);
+            if (np64 > 0x7fffffffLL) {
+                if (lane == 0) *overflow_flag = 1;
+                np64 = 0; // the product is refused; keep the remaining passes in range
+            }
+            nprod = (int)np64;
             if (nprod > SYM_HEAVY) {
                 if (lane == 0) heavy_list[atomicAdd(heavy_count, 1)] = row;
                 cnt = -1; // filled in by sym_count_heavy_kernel
@@ -1091,19 +1100,18 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     BSP_TRY(sc.alloc(&row_prod, (size_t)nbr + 1));
     BSP_TRY(sc.alloc(&row_prod_ptr, (size_t)nbr + 1));
     BSP_TRY(sc.alloc(&lists, (size_t)NCLASS * (nbr > 0 ? nbr : 1)));
-    BSP_TRY(sc.alloc(&counts, (size_t)NCLASS + 1)); // [NCLASS] = number of heavy rows of the count pass
+    BSP_TRY(sc.alloc(&counts, (size_t)NCLASS + 2)); // [NCLASS] = heavy rows of the count pass, [NCLASS+1] = per-row overflow flag
     BSP_TRY(sc.alloc(&heavy, (size_t)(nbr > 0 ? nbr : 1)));
     BSP_TRY(sc.alloc(&out->c_rowptr, (size_t)nbr + 1));
     BSP_CUDA(ctx, cudaMemsetAsync(row_cnt + nbr, 0, sizeof(int32_t), ctx->stream));
     BSP_CUDA(ctx, cudaMemsetAsync(row_prod + nbr, 0, sizeof(int32_t), ctx->stream));
-    BSP_CUDA(ctx, cudaMemsetAsync(counts, 0, (NCLASS + 1) * sizeof(int32_t), ctx->stream));
+    BSP_CUDA(ctx, cudaMemsetAsync(counts, 0, (NCLASS + 2) * sizeof(int32_t), ctx->stream));
 
     int grid = (nbr + SYM_WARPS - 1) / SYM_WARPS;
     const int max_grid = ctx->sm_count * 8;
     if (grid > max_grid) grid = max_grid;
     if (grid < 1) grid = 1;
-    // capacity classes of the shared-memory fill: tile products per row that fit next to the bitmaps
-        // capacity classes of the shared-memory fill (tile products / output tiles of a row):
+    // capacity classes of the shared-memory fill (tile products / output tiles of a row):
     // about 8 / 2 / 1 CTAs per SM; larger rows use the global-memory variant
     const int acap = 512;
     int caps[3] = {1536, 8200, 15000}, tcaps[3] = {1536, 6000, 15000};
@@ -1139,7 +1147,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
                                            (int)smem_count));
         sym_count_kernel<<<grid, SYM_THREADS, smem_count, ctx->stream>>>(
             nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, row_lo, row_hi, row_cnt, row_prod, heavy,
-            counts + NCLASS);
+            counts + NCLASS, counts + NCLASS + 1);
         BSP_LAUNCH_CHECK(ctx);
         {
             const size_t hb = (size_t)words * sizeof(uint32_t);
@@ -1164,14 +1172,26 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     int32_t *h_counts = (int32_t *)((char *)ctx->pinned + 16);
     BSP_CUDA(ctx, cudaMemcpyAsync(h_nnzb, out->c_rowptr + nbr, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
     BSP_CUDA(ctx, cudaMemcpyAsync(h_nprod, row_prod_ptr + nbr, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    BSP_CUDA(ctx, cudaMemcpyAsync(h_counts, counts, NCLASS * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    BSP_CUDA(ctx, cudaMemcpyAsync(h_counts, counts, (NCLASS + 2) * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
     bsp_trace_mark(ctx, "sym_scans");
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     out->nnzb_c = *h_nnzb;
     out->nprod = *h_nprod;
     int ncls[NCLASS];
     for (int c = 0; c < NCLASS; c++) ncls[c] = h_counts[c];
+    if (h_counts[NCLASS + 1])
+        BSP_FAIL(ctx, BSP_ERR_LIMIT, "a block row of the product has more than 2^31-1 tile products");
     if (out->nnzb_c < 0) BSP_FAIL(ctx, BSP_ERR_LIMIT, "product has more than 2^31-1 tiles");
+    if (out->nprod > 0x7fffffffLL) {
+        // nnzb(C) <= nprod, so the int32 row-pointer scan can only have wrapped past zero in this case:
+        // total the per-row tile counts again in 64 bits
+        int64_t *cnt64 = nullptr;
+        BSP_TRY(sc.alloc(&cnt64, (size_t)nbr + 1));
+        BSP_TRY(bsp_scan_i32_to_i64(ctx, row_cnt, cnt64, (int64_t)nbr + 1));
+        BSP_CUDA(ctx, cudaMemcpyAsync(h_nprod, cnt64 + nbr, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+        BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (*h_nprod > 0x7fffffffLL) BSP_FAIL(ctx, BSP_ERR_LIMIT, "product has more than 2^31-1 tiles");
+    }
     out->n_split = 0;
     out->split = nullptr;
     if (out->pair_budget > 0 && out->nprod > out->pair_budget) {

@@ -12,6 +12,8 @@
 #include <cstdlib>
 #include <deque>
 #include <mutex>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <thread>
 #include <vector>
@@ -31,7 +33,13 @@ inline const char *parse_u64(const char *p, const char *e, uint64_t *v, bool *ok
     p = skip_ws(p, e);
     uint64_t x = 0;
     const char *s = p;
-    while (p < e && (unsigned)(*p - '0') <= 9u) { x = x * 10u + (uint64_t)(*p - '0'); p++; }
+    while (p < e && (unsigned)(*p - '0') <= 9u) {
+        const uint64_t d = (uint64_t)(*p - '0');
+        // beyond 2^64-1 the reference's ifstream >> sets failbit (cu:375-376): refuse instead of wrapping
+        if (x > (UINT64_MAX - d) / 10u) *ok = false;
+        x = x * 10u + d;
+        p++;
+    }
     if (p == s) *ok = false;
     *v = x;
     return p;
@@ -44,7 +52,8 @@ inline const char *parse_i32(const char *p, const char *e, int32_t *v, bool *ok)
     if (p < e && (*p == '-' || *p == '+')) { neg = (*p == '-'); p++; }
     uint64_t x;
     p = parse_u64(p, e, &x, ok);
-    *v = neg ? -(int32_t)x : (int32_t)x;
+    if (x > (neg ? 2147483648ull : 2147483647ull)) { *ok = false; x = 0; } // does not fit an int
+    *v = neg ? (int32_t)(0 - (int64_t)x) : (int32_t)x;
     return p;
 }
 
@@ -55,8 +64,9 @@ bool read_file(const char *path, std::string *out)
     fseek(f, 0, SEEK_END);
     long sz = ftell(f);
     fseek(f, 0, SEEK_SET);
-    out->resize((size_t)sz);
-    bool ok = sz == 0 || fread(&(*out)[0], 1, (size_t)sz, f) == (size_t)sz;
+    bool ok = sz >= 0;
+    try { out->resize(ok ? (size_t)sz : 0); } catch (const std::exception &) { ok = false; sz = 0; }
+    ok = ok && (sz == 0 || fread(&(*out)[0], 1, (size_t)sz, f) == (size_t)sz);
     fclose(f);
     return ok;
 }
@@ -143,6 +153,14 @@ const char *parse_header(const char *p, const char *e, int32_t *rows, int32_t *c
     return (ok && *blocks >= 0) ? p : nullptr;
 }
 
+// A body of `blocks` tiles has blocks*(2+k*k) tokens of at least one digit and one separator each:
+// a header that promises more than the file can hold is refused before anything is sized from it.
+bool body_can_hold(const char *p, const char *e, int64_t blocks, int32_t k)
+{
+    const uint64_t tokens = (uint64_t)blocks * (2u + (uint64_t)k * (uint64_t)k);
+    return tokens <= ((uint64_t)(e - p) + 1u) / 2u;
+}
+
 unsigned host_threads()
 {
     unsigned nt = std::thread::hardware_concurrency();
@@ -164,12 +182,20 @@ extern "C" int bsp_mat_read_text(bsp_ctx *ctx, const char *path, int32_t k, bsp_
     int32_t rows = 0, cols = 0, blocks = 0;
     const char *p = parse_header(buf.data(), e, &rows, &cols, &blocks);
     if (!p) BSP_FAIL(ctx, BSP_ERR_IO, "%s: malformed header", path);
+    if (!body_can_hold(p, e, blocks, k))
+        BSP_FAIL(ctx, BSP_ERR_IO, "%s: header announces %d tiles, the file is too short for them", path, blocks);
     const size_t kk = (size_t)k * k;
-    std::vector<int32_t> br((size_t)blocks), bc((size_t)blocks);
-    std::vector<uint64_t> v((size_t)blocks * kk);
-    const std::string why = parse_body(p, e, blocks, k, host_threads(), br.data(), bc.data(), v.data());
-    if (!why.empty()) BSP_FAIL(ctx, BSP_ERR_IO, "%s: %s", path, why.c_str());
-    return bsp_mat_from_coo(ctx, rows, cols, k, blocks, br.data(), bc.data(), v.data(), out);
+    try { // nothing may leave through the C boundary
+        std::vector<int32_t> br((size_t)blocks), bc((size_t)blocks);
+        std::vector<uint64_t> v((size_t)blocks * kk);
+        const std::string why = parse_body(p, e, blocks, k, host_threads(), br.data(), bc.data(), v.data());
+        if (!why.empty()) BSP_FAIL(ctx, BSP_ERR_IO, "%s: %s", path, why.c_str());
+        return bsp_mat_from_coo(ctx, rows, cols, k, blocks, br.data(), bc.data(), v.data(), out);
+    } catch (const std::bad_alloc &) {
+        BSP_FAIL(ctx, BSP_ERR_NOMEM, "%s: host allocation failed", path);
+    } catch (const std::exception &ex) {
+        BSP_FAIL(ctx, BSP_ERR_IO, "%s: %s", path, ex.what());
+    }
 }
 
 // ---- several files at once: parsing overlapped with upload and ingestion ----
@@ -238,6 +264,7 @@ extern "C" int bsp_mat_read_text_many(bsp_ctx *ctx, const char *const *paths, in
             const char *p = nullptr;
             if (!read_file(paths[file], &buf)) why = "cannot open";
             else if (!(p = parse_header(buf.data(), buf.data() + buf.size(), &S.rows, &S.cols, &blocks32))) why = "malformed header";
+            else if (!body_can_hold(p, buf.data() + buf.size(), blocks32, k)) why = "header announces more tiles than the file can hold";
             if (why.empty()) {
                 S.blocks = blocks32;
                 const size_t need = (size_t)S.blocks * (kk * 8 + 8) + 64;
