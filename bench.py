@@ -7,10 +7,13 @@ SpGEMM useful GFLOP/s; chain milliseconds as a secondary figure).
 
 A step is one pass of the hot path (symbolic + numeric) over one synthetic workload:
 BASELINE.json configs[1], a single A*B with n=65536, k=8, 1 % block density, uint64 entries.
-At N > 1 every rank multiplies its own block-row panel A_r (seed differs per rank) by the
-same B -- the row-panel sharding of a taller A, which needs no data-path collective --
-so per-GPU work is fixed ("weak") and value = products of all ranks / max-over-ranks time.
+At N > 1 the SAME product is sharded over the N GPUs by contiguous block-row panels balanced by
+tile products (bsp_panel_bounds; B replicated, no data-path collective):
+total work is fixed ("strong") and value = products of the whole job / max-over-ranks time.
 Useful ops = 2*k^3*nprod (one multiply + one add per inner step), SURVEY.md section 8d.
+Every figure carries the content checksum of its result and is compared with the CPU oracle's
+checksum of the same full-size workload (tests/golden/full_size.json, made by
+tests/golden/make_full_size.py); a mismatch ends the run with a non-zero exit code.
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -37,8 +40,55 @@ WORKLOADS = {
     "k16": (65536, 16, 0.02, "u64"),
     "k32": (65536, 32, 0.02, "u64"),   # the tile size of the reference's own published numbers (report.pdf)
 }
-# DRAM bytes of one numeric-kernel launch from the committed `ncu --set full` capture (not measured live)
-NCU_TRAFFIC_BYTES = {("cfg2", 8): 29629984000 + 19178306000}
+
+
+def ncu_traffic(workload, path_id):
+    """DRAM bytes of one numeric-kernel launch from the latest committed `ncu --set full` capture
+    (profiles/ncu_traffic.json names the capture, its date and the commit it was taken at)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            for e in json.load(f)["captures"]:
+                if e["workload"] == workload and e["numeric_path"] == path_id:
+                    return e["dram_bytes_read"] + e["dram_bytes_write"], "%s (%s, commit %s)" % (e["file"], e["date"], e["commit"])
+    except (OSError, KeyError, ValueError):
+        pass
+    return None, None
+
+
+def int_mac_peak():
+    """u64 multiply-accumulate ceiling of the numeric kernel's inner loop (tools/u64mac_peak.cu run on a B200)."""
+    try:
+        best = 0.0
+        with open(os.path.join(ROOT, "profiles", "r01_u64mac_peak.jsonl")) as f:
+            for ln in f:
+                e = json.loads(ln)
+                if e.get("variant") == "flagged":
+                    best = max(best, float(e["u64_mac_per_s"]))
+        return best or None
+    except (OSError, ValueError):
+        return None
+
+
+def load_golden():
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "full_size.json")) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
+
+
+class ParityError(SystemExit):
+    pass
+
+
+def check_golden(what, got_hex, want_hex):
+    """A bench figure whose result differs from the oracle's is not a figure: stop with exit code 3."""
+    if want_hex is None:
+        return "no golden for this configuration"
+    if got_hex != want_hex:
+        sys.stderr.write("bench.py: PARITY FAILURE in %s: checksum %s, oracle %s\n" % (what, got_hex, want_hex))
+        raise ParityError(3)
+    return "equal to the oracle's (tests/golden/full_size.json)"
 METRIC = "spgemm_useful_gflops"
 UNIT = "GFLOP/s"
 
@@ -54,8 +104,13 @@ def algorithmic_bytes(nnzb_a, nnzb_b, nnzb_c, G, k):
 
 
 def symbolic_bytes(nnzb_a, nprod, nnzb_c, G):
-    """SURVEY.md section 8d symbolic figure plus the pair lists this design writes."""
-    return 4 * nnzb_a + 4 * nprod + 4 * nnzb_c + 12 * (G + 1) + 8 * nprod + 8 * (nnzb_c + 1)
+    """A block columns, the B block columns of every row touched, C block columns, row pointers."""
+    return 4 * nnzb_a + 4 * nprod + 4 * nnzb_c + 12 * (G + 1)
+
+
+def pair_list_bytes(nprod, nnzb_c):
+    """What this design writes on top of 8d: 8 B per tile product and one 8 B offset per output tile."""
+    return 8 * nprod + 8 * (nnzb_c + 1)
 
 
 def measured_peak():
@@ -205,6 +260,61 @@ def cpu_reference_measure(n, k, d, steps, warmup, use_all_threads=True):
     return dict(value=flop / sec / 1e9, unit=UNIT, cores=cores, kind="port", sample=desc, seconds_hot_path=sec, nprod=nprod)
 
 
+REF_CHAIN = dict(n_mats=64, n=1024, k=4, half_band=4, density=0.5)  # the chain of CHAIN at 1/16 of its block rows
+
+
+def reference_chain_measure(ranks):
+    """The reference program (its own main: MPI split over `ranks` ranks through the fork+pipe shim,
+    helper2 per rank, rank-0 merge) on a REDUCED copy of the chain workload -- same generator, same
+    band, 64 matrices, n=1024 instead of 16384: the full chain's last product alone is 1.8e8 tile
+    products, hours of single-threaded host packing (cu:189-218).  Returns hot-path and end-to-end ms."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import bsp_gen
+    import orc
+    c = REF_CHAIN
+    G = c["n"] // c["k"]
+    mats = []
+    for i in range(c["n_mats"]):
+        br, bc = bsp_gen.banded_pattern(G, c["half_band"], c["density"], 5000 + i)
+        v = bsp_gen.values(5000 + i, br.size * c["k"] * c["k"], "small").reshape(-1, c["k"], c["k"])
+        mats.append(orc.OMat.from_coo(c["n"], c["n"], c["k"], br, bc, v))
+    variant = "ref_host_timed" if orc.have_ref("ref_host_timed") else None
+    if variant is None:
+        t0 = time.perf_counter()
+        orc.chain(mats, ranks=ranks)
+        sec = time.perf_counter() - t0
+        return {"ms": sec * 1e3, "kind": "port", "ranks": ranks, "workload": "reduced chain %r" % (c,)}
+    with tempfile.TemporaryDirectory(prefix="bsp_cpu_chain_") as folder:
+        orc.write_folder(folder, mats, c["k"])
+        r = orc.run_ref(folder, ranks=ranks, variant=variant, keep_output=False)
+    if r["returncode"] != 0:
+        raise RuntimeError("reference chain run failed: " + r["stderr"][-300:])
+    return {"ms": (max(r["time_taken"]) if r["time_taken"] else float("nan")) * 1e3, "hot_path_ms_rank0": sum(r["phases"].values()) * 1e3,
+            "kind": "reference", "ranks": ranks, "products": len(r["multiplying"]),
+            "workload": "reduced chain %r, values in [1,1000]; ms = the reference's own 'time taken' line (cu:679, includes its text I/O)" % (c,)}
+
+
+def reference_cfg1_measure():
+    """BASELINE.json configs[0] in full (n=1024, k=4, 5 %): the one configuration the reference runs as it is."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import bsp_gen
+    import orc
+    n, k, d, _ = WORKLOADS["cfg1"]
+    a = bsp_gen.random_matrix(n, n, k, d, 1000, "u64")
+    b = bsp_gen.random_matrix(n, n, k, d, 1001, "u64")
+    nprod = int(np.bincount(b[3], minlength=n // k)[a[4]].sum())
+    if not orc.have_ref("ref_host_timed"):
+        t0 = time.perf_counter()
+        orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))
+        sec = time.perf_counter() - t0
+        return {"gflops": 2.0 * k ** 3 * nprod / sec / 1e9, "hot_path_ms": sec * 1e3, "kind": "port", "nprod": nprod}
+    with tempfile.TemporaryDirectory(prefix="bsp_cpu_cfg1_") as folder:
+        orc.write_folder(folder, [orc.OMat.from_coo(*a), orc.OMat.from_coo(*b)], k)
+        hot, tt, _ = run_reference_once(folder, "ref_host_timed", 1)
+    return {"gflops": 2.0 * k ** 3 * nprod / hot / 1e9, "hot_path_ms": hot * 1e3, "end_to_end_ms": tt * 1e3 if tt else None,
+            "kind": "reference", "nprod": nprod, "workload": "configs[0] in full: n=%d, k=%d, %g%% density, single rank as shipped" % (n, k, d * 100)}
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -215,10 +325,17 @@ def reference_arm(args):
     cb = cpu_reference_measure(n, k, d, steps, warm)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": steps, "warmup": warm, "ms_per_step": cb["seconds_hot_path"] * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": workload_name(n, k, d), "sample": cb["sample"]},
+            "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": workload_name(n, k, d), "sample": cb["sample"],
+                       "note": "the reference cannot shard one product (SURVEY.md 8e): at every N this line is its single-rank "
+                               "rate on the sample; its N-rank figure is the chain below"},
             "cpu_baseline": {kk: cb[kk] for kk in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    for key, fn in (("chain", lambda: reference_chain_measure(max(1, args.gpus))), ("cfg1", reference_cfg1_measure)):
+        try:
+            line[key] = fn()
+        except Exception as ex:  # reported baselines, never load-bearing
+            line[key] = {"unavailable": str(ex)[:200]}
     print(json.dumps(line))
     return 0
 
@@ -241,20 +358,42 @@ def chain_matrix(i):
     return c["n"], c["n"], c["k"], br, bc, v
 
 
-def run_chain(torch, dist, ctx, rank, world, steps, warmup):
+def make_comm(torch, dist, ctx, rank, world):
+    """One NCCL communicator of the C ABI per rank (bsp_comm_create); the rendezvous token travels over
+    torch.distributed, which the bench has anyway for its barriers."""
+    import bspgemm
+    tok = torch.zeros(bspgemm.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        tok.copy_(torch.frombuffer(bytearray(bspgemm.comm_unique_id()), dtype=torch.uint8))
+    dist.broadcast(tok, 0)
+    torch.cuda.synchronize()
+    return bspgemm.Comm(ctx, bytes(tok.cpu().numpy().tobytes()), world, rank)
+
+
+def summed_checksum(torch, dist, world, mat, rows, cols, k):
+    """Checksum of a matrix spread over the ranks as row panels: tile sums and tile counts add up."""
+    import bspgemm
+    body = mat.checksum_body() if mat is not None else 0
+    nnzb = mat.nnzb if mat is not None else 0
+    v = torch.tensor([body - (1 << 64) if body >= (1 << 63) else body, nnzb], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(v, op=dist.ReduceOp.SUM)  # int64 addition wraps: the sum modulo 2^64
+    body_all, nnzb_all = int(v[0].item()) & ((1 << 64) - 1), int(v[1].item())
+    return "%016x" % bspgemm.checksum_finish(rows, cols, k, 8, nnzb_all, body_all), nnzb_all
+
+
+def run_chain(torch, dist, ctx, comm, rank, world, steps, warmup, golden):
     """Chain of 64 matrices split into contiguous sub-chains over the ranks exactly as the
     reference splits it over MPI ranks (cu:438-456), local pairwise tree per rank, then the
-    step-doubling merge of the partial products over NCCL send/recv (strong scaling: the
-    chain is fixed).  Returns dict for the JSON line (rank 0) or None."""
+    step-doubling merge of the partial products through the C ABI (bsp_chain_distributed: NCCL
+    send/recv, every product sharded over its subtree).  Strong scaling: the chain is fixed.
+    Returns dict for the JSON line (rank 0) or None."""
     import bsp_dist
     import bspgemm
     parts = bsp_dist.split_chain(CHAIN["n_mats"], world)
     mine = parts[rank] if rank < len(parts) else None
     mats = [ctx.matrix_from_coo(*chain_matrix(i)) for i in range(mine[0], mine[1] + 1)] if mine else []
     nprod = 0
-    sent = 0
-    gb = bsp_dist.GroupBroadcaster(dist, torch, len(parts), "cuda") if world > 1 else None
-    tp = bsp_dist.GpuTransport(torch, dist, ctx, len(parts)) if world > 1 else None
 
     def sync():
         torch.cuda.synchronize()
@@ -263,100 +402,66 @@ def run_chain(torch, dist, ctx, rank, world, steps, warmup):
         torch.cuda.synchronize()
 
     def one():
-        nonlocal nprod, sent
+        nonlocal nprod
         st = bspgemm.Stats()
-        tr = bsp_dist._phase_tracer(rank)
-        partial = ctx.helper2(mats, stats=st) if mats else None
-        tr("local sub-chain")
-        nprod = st.nprod
         if world == 1:
-            return partial
-
-        def mul(a, b):
-            nonlocal nprod
-            s2 = bspgemm.Stats()
-            c = ctx.helper(a, b, stats=s2)
-            nprod += s2.nprod
-            return c
-
-        def send(m, dst):
-            nonlocal sent
-            pl = bsp_dist.matrix_to_payload(torch, m)
-            sent += pl.nbytes
-            bsp_dist.send_payload(dist, pl, dst)
-
-        def recv(src):
-            return bsp_dist.payload_to_matrix(torch, ctx, bsp_dist.recv_payload(dist, torch, src, "cuda"))
-
-        def mul_panel(a, b, rng):
-            nonlocal nprod
-            s2 = bspgemm.Stats()
-            c = ctx.helper(a, b, stats=s2, panel=rng)
-            nprod += s2.nprod
-            return c
-
-        def send_rows(m, lo, hi, dst):
-            nonlocal sent
-            pl = bsp_dist.slice_rows_payload(torch, bsp_dist.matrix_to_payload(torch, m), lo, hi)
-            sent += pl.nbytes
-            bsp_dist.send_payload(dist, pl, dst)
-
-        def bcast(m, src, grp):
-            nonlocal sent
-            pl = bsp_dist.matrix_to_payload(torch, m) if m is not None else None
-            if pl is not None:
-                sent += pl.nbytes
-            return bsp_dist.payload_to_matrix(torch, ctx, gb.bcast(pl, src, grp))
-        mode = os.environ.get("BSP_CHAIN_MERGE", "distributed")
-        if mode == "rank0":  # the reference's shape: the receiver multiplies alone
-            return bsp_dist.tree_merge(rank, len(parts), partial, mul, send, recv)
-        if mode == "panels":  # sharded products, gathered on the group leader after every level
-            return bsp_dist.tree_merge_panels(rank, len(parts), partial, send, recv, send_rows, bcast,
-                                              lambda m: bsp_dist.device_row_weights(torch, m), mul_panel, ctx.concat_panels)
-        tp.sent = 0
-        out = bsp_dist.tree_merge_distributed(rank, len(parts), partial, tp.send, tp.recv, tp.send_rows, tp.bcast,
-                                              tp.row_weights, mul_panel, ctx.concat_panels, gather=tp.gather)
-        sent = tp.sent
+            out = ctx.helper2(mats, stats=st)
+        else:
+            out = comm.chain(mats, stats=st, log_base=mine[0] if mine else 0)
+        nprod = st.nprod
         return out
 
     res = None
     for _ in range(warmup):
         res = one()
     sync()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(torch.cuda.current_stream())
-    for _ in range(steps):
-        sent = 0
+    sent0 = comm.bytes_sent if comm else 0
+    stream = torch.cuda.current_stream()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    evs[0].record(stream)
+    for i in range(steps):
         res = one()
-    e1.record(torch.cuda.current_stream())
+        evs[i + 1].record(stream)
     sync()
-    t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device="cuda")
+    per_step = [evs[i].elapsed_time(evs[i + 1]) for i in range(steps)]
+    sent = ((comm.bytes_sent - sent0) // steps) if comm else 0
+    t = torch.tensor([evs[0].elapsed_time(evs[steps]) / steps], dtype=torch.float64, device="cuda")
     w = torch.tensor([float(nprod)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(w, op=dist.ReduceOp.SUM)
+    for m in mats:
+        m.free()
     if rank != 0:
         return None
     k = CHAIN["k"]
-    return {"ms": t.item(), "unit": "ms", "n_gpus": world, "scaling": "strong",
-            "workload": "chain of %d matrices, n=%d, k=%d, banded pattern (half-band %d blocks, %.0f%% filled), uint64; "
-                        "sub-chains of %d per GPU, NCCL tree merge, every product row-panel sharded over its subtree, panels stay distributed" % (CHAIN["n_mats"], CHAIN["n"], k, CHAIN["half_band"],
-                                                                      CHAIN["density"] * 100, CHAIN["n_mats"] // max(len(parts), 1)),
-            "products": CHAIN["n_mats"] - 1, "nprod_total": int(w.item()), "result_nnzb": int(res.nnzb),
-            "useful_gflops": 2.0 * k ** 3 * w.item() / (t.item() * 1e-3) / 1e9,
-            "rank0_bytes_sent_per_step": int(sent)}
+    cs = "%016x" % res.checksum()
+    want = golden.get("chain", {}).get("ranks", {}).get(str(len(parts)), {})
+    verdict = check_golden("chain (%d ranks)" % len(parts), cs, want.get("checksum"))
+    out = {"ms": t.item(), "unit": "ms", "n_gpus": world, "scaling": "strong", "steps": steps, "warmup": warmup,
+           "per_step_ms_rank0": [round(x, 3) for x in per_step],
+           "workload": "chain of %d matrices, n=%d, k=%d, banded pattern (half-band %d blocks, %.0f%% filled), uint64; "
+                       "sub-chains of %d per GPU, merge by bsp_chain_distributed (NCCL send/recv, every product row-panel "
+                       "sharded over its subtree, panels stay distributed)" % (CHAIN["n_mats"], CHAIN["n"], k, CHAIN["half_band"],
+                                                                              CHAIN["density"] * 100, CHAIN["n_mats"] // max(len(parts), 1)),
+           "products": CHAIN["n_mats"] - 1, "nprod_total": int(w.item()), "result_nnzb": int(res.nnzb),
+           "checksum": cs, "checksum_vs_oracle": verdict,
+           "useful_gflops": 2.0 * k ** 3 * w.item() / (t.item() * 1e-3) / 1e9,
+           "rank0_bytes_sent_per_step": int(sent)}
+    res.free()
+    return out
 
 
 # --------------------------------------------------------------------------------------------
 # secondary figure: power-law pattern, row-panel sharded single product (BASELINE.json configs[3])
 # --------------------------------------------------------------------------------------------
 
-def run_rmat(torch, dist, ctx, rank, world, steps):
+def run_rmat(torch, dist, ctx, rank, world, steps, golden):
     """R-MAT block pattern (scale 15 = 32768 block rows, edge factor 16, a/b/c/d = .57/.19/.19/.05),
     n=262144, k=8.  Every rank holds A and B (same seeds), multiplies ONE block-row panel of A by B;
-    panels are contiguous and balanced by tile products per block row.  No collective on the data
-    path; the product stays distributed by panels.  Strong scaling: the product is fixed."""
-    import bsp_dist
+    panels are contiguous and balanced by tile products per block row (bsp_panel_bounds, on the
+    device).  No collective on the data path; the product stays distributed by panels.  Strong
+    scaling: the product is fixed."""
     import bsp_gen
     import bspgemm
     scale, k = 15, 8
@@ -366,20 +471,23 @@ def run_rmat(torch, dist, ctx, rank, world, steps):
         br, bc = bsp_gen.rmat_pattern(scale, 16, seed)
         v = bsp_gen.values(seed, br.size * k * k, "u64").reshape(-1, k, k)
         mats.append((G * k, G * k, k, br, bc, v))
-    rowlen_b = np.bincount(mats[1][3], minlength=G)
-    row_work = np.bincount(mats[0][3], weights=rowlen_b[mats[0][4]], minlength=G)
-    bounds = bsp_dist.balanced_panels(row_work, world)
     A, B = ctx.matrix_from_coo(*mats[0]), ctx.matrix_from_coo(*mats[1])
+    del mats
+    bounds = ctx.panel_bounds(A, B, world)
     st = bspgemm.Stats()
-    ms = []
+    ms, sym, C = [], [], None
     for i in range(steps + 2):
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-        ctx.helper(A, B, stats=st, panel=(bounds[rank], bounds[rank + 1])).free()
+        if C is not None:
+            C.free()
+        C = ctx.helper(A, B, stats=st, panel=(bounds[rank], bounds[rank + 1]) if world > 1 else None)
         if i >= 2:
-            ms.append(st.ms_total)
-    mine = torch.tensor([sum(ms) / len(ms), float(st.nprod), float(st.nnzb_c)], dtype=torch.float64, device="cuda")
+            ms.append(st.ms_total); sym.append(st.ms_symbolic)
+    cs, nnzb_all = summed_checksum(torch, dist, world, C, G * k, G * k, k)
+    C.free()
+    mine = torch.tensor([sum(ms) / len(ms), float(st.nprod), sum(sym) / len(sym)], dtype=torch.float64, device="cuda")
     allv = [torch.zeros_like(mine) for _ in range(world)]
     if world > 1:
         dist.all_gather(allv, mine)
@@ -390,11 +498,13 @@ def run_rmat(torch, dist, ctx, rank, world, steps):
         return None
     t = [x[0].item() for x in allv]
     nprod = sum(x[1].item() for x in allv)
+    verdict = check_golden("R-MAT product", cs, golden.get("rmat", {}).get("checksum"))
     return {"ms": max(t), "unit": "ms", "n_gpus": world, "scaling": "strong",
             "workload": "R-MAT block pattern scale %d (n=%d, k=%d), A*B row-panel sharded x%d, panels balanced by tile products"
                         % (scale, G * k, k, world),
-            "per_gpu_ms": [round(x, 3) for x in t], "max_over_mean": max(t) / (sum(t) / len(t)),
-            "nprod_total": int(nprod), "nnzb_c_total": int(sum(x[2].item() for x in allv)),
+            "per_gpu_ms": [round(x, 3) for x in t], "per_gpu_symbolic_ms": [round(x[2].item(), 3) for x in allv],
+            "max_over_mean": max(t) / (sum(t) / len(t)),
+            "nprod_total": int(nprod), "nnzb_c_total": int(nnzb_all), "checksum": cs, "checksum_vs_oracle": verdict,
             "useful_gflops": 2.0 * k ** 3 * nprod / (max(t) * 1e-3) / 1e9}
 
 
@@ -469,10 +579,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 3)")
     ap.add_argument("--no-chain", action="store_true")
-    ap.add_argument("--rmat", action="store_true", help="also run the R-MAT row-panel figure (default: only when --gpus > 1)")
+    ap.add_argument("--rmat", action="store_true", help="(kept for old command lines: the R-MAT figure always runs)")
     ap.add_argument("--no-rmat", action="store_true")
     ap.add_argument("--no-float", action="store_true")
-    ap.add_argument("--chain-steps", type=int, default=2)
+    ap.add_argument("--chain-steps", type=int, default=5, help="timed chain steps (at least 5, after 3 warm-ups)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -498,13 +608,18 @@ def main():
     warmup = max(args.warmup, 3)
     n, k, d, kind = WORKLOADS[args.workload]
     G = n // k
+    golden = load_golden()
 
     stream = torch.cuda.Stream()
     with torch.cuda.stream(stream):
         ctx = bspgemm.Context(local, stream=stream.cuda_stream)
-        a = bsp_gen.random_matrix(n, n, k, d, 1000 + 7919 * rank, kind)  # this rank's row panel of A
-        b = bsp_gen.random_matrix(n, n, k, d, 1001, kind)               # B, replicated
+        comm = make_comm(torch, dist, ctx, rank, world) if world > 1 else None
+        a = bsp_gen.random_matrix(n, n, k, d, 1000, kind)  # A and B of the ONE product all ranks share
+        b = bsp_gen.random_matrix(n, n, k, d, 1001, kind)
         A, B = ctx.matrix_from_coo(*a), ctx.matrix_from_coo(*b)
+        # this rank's block-row panel (balanced by tile products on the device; whole product at N = 1)
+        bounds = ctx.panel_bounds(A, B, world)
+        panel = (bounds[rank], bounds[rank + 1]) if world > 1 else None
 
         def barrier():
             torch.cuda.synchronize()
@@ -514,7 +629,7 @@ def main():
 
         st = bspgemm.Stats()
         for _ in range(warmup):
-            ctx.helper(A, B, stats=st).free()
+            ctx.helper(A, B, stats=st, panel=panel).free()
         barrier()
         sampler = ClockSampler(local)
         if rank == 0:
@@ -522,9 +637,12 @@ def main():
         launches0 = ctx.launch_count()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         num_ms, sym_ms = [], []
+        Cres = None
         ev0.record(stream)
         for _ in range(args.steps):
-            ctx.helper(A, B, stats=st).free()
+            if Cres is not None:
+                Cres.free()
+            Cres = ctx.helper(A, B, stats=st, panel=panel)
             num_ms.append(st.ms_numeric); sym_ms.append(st.ms_symbolic)
         ev1.record(stream)
         barrier()
@@ -532,30 +650,29 @@ def main():
         launches = ctx.launch_count() - launches0
         ms_total = ev0.elapsed_time(ev1)
         t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
-        work = torch.tensor([float(st.nprod)], dtype=torch.float64, device="cuda")
+        work = torch.tensor([float(st.nprod), float(st.nnzb_c)], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dist.all_reduce(work, op=dist.ReduceOp.SUM)
         ms_step = t.item() / args.steps
-        nprod_all = work.item()
+        nprod_all, nnzb_c_all = work[0].item(), int(work[1].item())
         value = 2.0 * k ** 3 * nprod_all / (ms_step * 1e-3) / 1e9
+        # parity of what was just timed: the panels' checksums add up to the oracle's checksum of the product
+        head_cs, _ = summed_checksum(torch, dist, world, Cres, n, n, k)
+        Cres.free()
+        head_verdict = None
+        if rank == 0:
+            want = golden.get(args.workload, {}).get("checksum") if args.workload == "cfg2" else None
+            head_verdict = check_golden("headline product", head_cs, want)
 
-        # end to end through the C ABI with HOST buffers: upload A and B, multiply, download C
+        # end to end through the C ABI with HOST buffers: upload this rank's rows of A and all of B, multiply,
+        # download the rank's part of C.  At N > 1 the ranks share one host's PCIe and memory bandwidth.
         e2e = None
         if not args.no_e2e:
-            # Host memory bound: the result of one product is 19.5 GB; with N ranks on one host the
-            # pinned output buffers would be N times that.  At N > 1 each rank therefore runs the
-            # end-to-end call on 1/N of its block rows (all of B), which keeps the host footprint of
-            # the whole job at one result; the figure is still work / time through the same call.
-            frac = world
-            keep = a[3] < (G // frac)
+            keep = (a[3] >= bounds[rank]) & (a[3] < bounds[rank + 1])
             ea = (a[0], a[1], a[2], a[3][keep], a[4][keep], a[5][keep])
-            st_e = bspgemm.Stats()
-            eA = ctx.matrix_from_coo(*ea)
-            ctx.helper(eA, B, stats=st_e).free()
-            eA.free()
-            nc = int(st_e.nnzb_c)
-            e_nprod = float(st_e.nprod)
+            nc = int(st.nnzb_c)
+            e_nprod = float(st.nprod)
             old_mask, affinity_note = gpu_local_affinity(torch, local)
             pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)  # noqa: E731
             ha = [pin(ea[3].shape, torch.int32), pin(ea[4].shape, torch.int32), pin(ea[5].size, torch.int64)]
@@ -585,20 +702,20 @@ def main():
                    "steps": esteps, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "api": "bsp_multiply_host (pinned host buffers in, pinned host buffers out)",
                    "cpu_affinity": affinity_note,
-                   "rows_per_rank": "all block rows" if frac == 1 else
-                   "block rows [0, G/%d) of each rank's A (host memory bound: one 19.5 GB result per host)" % frac}
+                   "rows_per_rank": "all block rows" if world == 1 else
+                   "each rank its block-row panel of A and all of B (bytes are rank 0's; the ranks share one host)"}
             del ha, hb, ho
             if old_mask is not None:
                 os.sched_setaffinity(0, old_mask)
 
+        A.free(); B.free()
         chain = None
         if not args.no_chain:
-            A.free(); B.free()
-            chain = run_chain(torch, dist, ctx, rank, world, max(1, args.chain_steps), 1)
+            chain = run_chain(torch, dist, ctx, comm, rank, world, max(5, args.chain_steps), 3, golden)
 
         rmat = None
-        if (args.rmat or world > 1) and not args.no_rmat:
-            rmat = run_rmat(torch, dist, ctx, rank, world, 3)
+        if not args.no_rmat:
+            rmat = run_rmat(torch, dist, ctx, rank, world, 3, golden)
 
         floats = None
         if world == 1 and not args.no_float:
@@ -606,29 +723,41 @@ def main():
 
         if rank == 0:
             peak, peak_src = measured_peak()
-            alg = algorithmic_bytes(st.nnzb_a, st.nnzb_b, st.nnzb_c, G, k)
+            # the launch of rank 0: its panel of A, all of B, its panel of C
+            alg = algorithmic_bytes(st.nnzb_a if world == 1 else int(keep_count(a, bounds, rank)), st.nnzb_b, st.nnzb_c, G, k)
             k_ms = sum(num_ms) / len(num_ms)
             s_ms = sum(sym_ms) / len(sym_ms)
             ach = alg / (k_ms * 1e-3) / 1e9
             sb = symbolic_bytes(st.nnzb_a, st.nprod, st.nnzb_c, G)
+            pl = pair_list_bytes(st.nprod, st.nnzb_c)
+            traffic, traffic_src = ncu_traffic(args.workload, st.numeric_path) if world == 1 else (None, None)
+            mac_peak = int_mac_peak()
+            mac_rate = k ** 3 * st.nprod / (k_ms * 1e-3)
             line = {
                 "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
-                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "u64", "data": "synthetic",
-                "config": {"workload": workload_name(n, k, d), "parallelism": "row-panel x%d (B replicated, no collective)" % world,
+                "config": {"workload": workload_name(n, k, d),
+                           "parallelism": "one product, %d block-row panel(s) balanced by tile products (B replicated, no collective)" % world,
                            "l2": "inputs (%.2f GB) and output (%.2f GB per step) exceed the 126 MB L2; no explicit flush"
-                                 % ((st.nnzb_a + st.nnzb_b) * k * k * 8 / 1e9, st.nnzb_c * k * k * 8 / 1e9),
-                           "nnzb_a": st.nnzb_a, "nnzb_b": st.nnzb_b, "nnzb_c": st.nnzb_c, "nprod": st.nprod,
-                           "numeric_path": st.numeric_path, "exact_refolds": st.exact_refolds},
+                                 % ((st.nnzb_a + st.nnzb_b) * k * k * 8 / 1e9, nnzb_c_all * k * k * 8 / 1e9),
+                           "nnzb_a": st.nnzb_a, "nnzb_b": st.nnzb_b, "nnzb_c": nnzb_c_all, "nprod": int(nprod_all),
+                           "panel_bounds": bounds, "numeric_path": st.numeric_path, "exact_refolds": st.exact_refolds},
+                "checksum": head_cs, "checksum_vs_oracle": head_verdict,
                 "phases_ms": {"symbolic": s_ms, "numeric": k_ms},
-                "roofline": {"bound": "hbm", "kernel": "numeric pass (tile multiply-accumulate)", "achieved": ach,
+                "roofline": {"bound": "hbm", "kernel": "numeric pass (tile multiply-accumulate), rank 0's launch", "achieved": ach,
                              "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                             "traffic": NCU_TRAFFIC_BYTES.get((args.workload, world == 1 and st.numeric_path)),
-                             "traffic_source": "profiles/r01_ncu_full_v11_numeric_raw.csv (dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
+                             "traffic": traffic, "traffic_source": traffic_src,
                              "algorithmic_bytes": alg, "peak_source": peak_src,
-                             "useful_u64_mac_per_s": k ** 3 * st.nprod / (k_ms * 1e-3)},
+                             "useful_u64_mac_per_s": mac_rate, "int_mac_peak": mac_peak,
+                             "int_mac_frac": (mac_rate / mac_peak) if mac_peak else None,
+                             "int_mac_peak_source": "profiles/r01_u64mac_peak.jsonl (tools/u64mac_peak.cu: the kernel's inner loop on "
+                                                    "registers and shared memory only, best of its grid sizes; not a driver-measured peak)"},
                 "roofline_symbolic": {"bound": "hbm", "achieved": sb / (s_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                                      "frac": sb / (s_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes": sb},
+                                      "frac": sb / (s_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes": sb,
+                                      "bytes_with_pair_lists": sb + pl,
+                                      "frac_with_pair_lists": (sb + pl) / (s_ms * 1e-3) / 1e9 / peak,
+                                      "frac_of_nominal_8TBs": sb / (s_ms * 1e-3) / 1e9 / 8000.0},
                 "gpu_launches": int(launches), "clocks": clocks,
             }
             if e2e:
@@ -647,10 +776,16 @@ def main():
                     line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": str(ex)}
             real_stdout.write(json.dumps(line) + "\n")
             real_stdout.flush()
+        if comm:
+            comm.close()
         ctx.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def keep_count(a, bounds, rank):
+    return int(((a[3] >= bounds[rank]) & (a[3] < bounds[rank + 1])).sum())
 
 
 if __name__ == "__main__":

@@ -189,6 +189,56 @@ int bsp_prune_zero_noalloc(bsp_ctx *ctx, int32_t k, int32_t nbrows, int64_t nnzb
                            int32_t *d_rowptr_out, int32_t *d_colidx_out, uint64_t *d_vals_out,
                            int64_t *nnzb_out);
 
+/* ---- several GPUs: NCCL transport and the distributed chain (replaces cu:438-571) ------ */
+
+/* One communicator per GPU, held by the process (or host thread) that drives it.  NCCL is bound
+ * at run time (libnccl.so.2); without it these calls return BSP_ERR_CUDA.  A communicator is used
+ * with one context; its calls are collective where stated and run on the context's stream. */
+typedef struct bsp_comm bsp_comm;
+#define BSP_COMM_ID_BYTES 128
+/* Rank 0 makes the rendezvous token (ncclGetUniqueId) and hands it to the other ranks by any
+ * means (the reference's MPI_Init, cu:404, has no counterpart here); cap >= BSP_COMM_ID_BYTES. */
+int bsp_comm_unique_id(void *id, size_t cap);
+/* Collective over all ranks (ncclCommInitRank). */
+int bsp_comm_create(bsp_ctx *ctx, const void *id, int nranks, int rank, bsp_comm **out);
+/* Wrap an ncclComm_t the caller already owns (it is not destroyed with the handle). */
+int bsp_comm_adopt(bsp_ctx *ctx, void *nccl_comm, int nranks, int rank, bsp_comm **out);
+void bsp_comm_destroy(bsp_ctx *ctx, bsp_comm *comm);
+int bsp_comm_info(const bsp_comm *comm, int *nranks, int *rank, int64_t *bytes_sent);
+
+/* Move one matrix (uint64 or float32 tiles) between two ranks: a fixed-size header, then row
+ * pointers, block columns and tile values in one NCCL group.  Replaces MPI_Send of header / keys /
+ * values (cu:471-506) and MPI_Recv + map rebuild (cu:513-551).  bsp_mat_send returns when the
+ * matrix may be changed; bsp_mat_recv waits once on the host to size the body, as cu:513-520 does. */
+int bsp_mat_send(bsp_ctx *ctx, bsp_comm *comm, const bsp_mat *m, int peer);
+int bsp_mat_recv(bsp_ctx *ctx, bsp_comm *comm, int peer, bsp_mat **out);
+/* Collective: the root passes `in`, every other rank receives a copy in *out (no reference
+ * counterpart: the reference never replicates an operand). */
+int bsp_mat_bcast(bsp_ctx *ctx, bsp_comm *comm, int root, const bsp_mat *in, bsp_mat **out);
+
+/* Collective: the ranks' block-row panels of one product (bsp_spgemm_panel over disjoint,
+ * rank-ascending row ranges) are concatenated on `root` (*out there, NULL elsewhere); received
+ * straight into the result's arrays.  The "gather for file output" step of row-panel sharding. */
+int bsp_gather_panels(bsp_ctx *ctx, bsp_comm *comm, const bsp_mat *panel, int root, bsp_mat **out);
+
+/* Collective: the whole multi-rank chain product of main (cu:438-571).  Every rank passes ITS
+ * sub-chain (mats[0..n_local-1], the split of cu:438-456 is the caller's: rank r loads matrices
+ * [r*(N/P), (r+1)*(N/P)), the last rank the remainder; when N < P rank 0 passes all and the others
+ * none, cu:612-616); log / log_base as in bsp_chain.  The sub-chain is reduced locally, then the P
+ * partial products are reduced with the association tree of rank 0's helper2 (cu:569-571) as a
+ * step-doubling tree in which EVERY product is sharded by block rows over the ranks of its subtree
+ * and stays distributed between levels (the reference multiplies the partials on rank 0 alone).
+ * Same tree, same per-element fold order: the result on rank 0 (*out; NULL elsewhere) is
+ * bit-identical to the P-rank reference run.  Zero tiles are kept (prune on rank 0 afterwards). */
+int bsp_chain_distributed(bsp_ctx *ctx, bsp_comm *comm, bsp_mat *const *mats, int32_t n_local, int32_t log_base,
+                          bsp_mat **out, bsp_stats *stats, char *log, size_t log_cap);
+
+/* Contiguous block-row panels of A*B for `nparts` GPUs, balanced by the work of every block row
+ * (tile products, from the operands' row pointers, computed on the device): bounds[0..nparts],
+ * host array.  Panel p is rows [bounds[p], bounds[p+1]); feed it to bsp_spgemm_panel.  No reference
+ * counterpart (the reference cannot split one product). */
+int bsp_panel_bounds(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t nparts, int32_t *bounds);
+
 /* ---- text format of the reference (either side of the path) -------------------------- */
 
 /* Parse one "matrixI" file (rows cols / blocks / {brow bcol / k*k values}), cu:345-383. */
@@ -214,6 +264,11 @@ int bsp_mat_read_text_many(bsp_ctx *ctx, const char *const *paths, int32_t n, in
  * BASELINE.json configs[1], where the reference's only comparison is a diff of 35-50 GB text
  * files (cu:595-608) -- can be compared by value.  Defined in csrc/bsp_checksum.cu. */
 int bsp_mat_checksum(bsp_ctx *ctx, const bsp_mat *m, uint64_t *out);
+/* The two halves of the definition, for a matrix that is spread over several GPUs as row panels:
+ * the order-independent sum over this panel's tiles (add the ranks' sums modulo 2^64), and the
+ * final mix of that sum with the header of the whole matrix. */
+int bsp_mat_checksum_body(bsp_ctx *ctx, const bsp_mat *m, uint64_t *body);
+uint64_t bsp_checksum_finish(int32_t rows, int32_t cols, int32_t k, int32_t esize, int64_t nnzb, uint64_t body);
 
 /* Binary file: 64-byte header ("BSPMAT01", rows, cols, k, element size, tile count, checksum),
  * then brow[], bcol[] (int32, tiles in (brow, bcol) order) and the tile values.  The reader

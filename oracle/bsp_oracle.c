@@ -231,7 +231,12 @@ orc_mat *orc_multiply_mt(const orc_mat *a, const orc_mat *b, int64_t *nprod_out,
 
 orc_mat *orc_multiply(const orc_mat *a, const orc_mat *b, int64_t *nprod_out)
 {
-    return orc_multiply_mt(a, b, nprod_out, 1);
+    /* ORC_THREADS=n spreads the emulated kernel loop of every product (also those inside orc_chain /
+     * orc_chain_ranks) over n threads; each output tile is still folded by one thread in reference
+     * order, so the result does not depend on n (used by tests/golden/make_full_size.py). */
+    const char *e = getenv("ORC_THREADS");
+    int nt = e ? atoi(e) : 1;
+    return orc_multiply_mt(a, b, nprod_out, nt > 0 ? nt : 1);
 }
 
 /* helper2 (cu:287-327): adjacent pairs at each level, odd tail carried unchanged. */

@@ -76,6 +76,20 @@ _SIGNATURES = {
     "bsp_mat_write_text": (C.c_int, [_VP, _VP, C.c_char_p]),
     "bsp_mat_read_text_many": (C.c_int, [_VP, C.POINTER(C.c_char_p), C.c_int32, C.c_int32, C.POINTER(_VP)]),
     "bsp_mat_checksum": (C.c_int, [_VP, _VP, C.POINTER(C.c_uint64)]),
+    "bsp_mat_checksum_body": (C.c_int, [_VP, _VP, C.POINTER(C.c_uint64)]),
+    "bsp_checksum_finish": (C.c_uint64, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_uint64]),
+    "bsp_comm_unique_id": (C.c_int, [_VP, C.c_size_t]),
+    "bsp_comm_create": (C.c_int, [_VP, _VP, C.c_int, C.c_int, C.POINTER(_VP)]),
+    "bsp_comm_adopt": (C.c_int, [_VP, _VP, C.c_int, C.c_int, C.POINTER(_VP)]),
+    "bsp_comm_destroy": (None, [_VP, _VP]),
+    "bsp_comm_info": (C.c_int, [_VP, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64)]),
+    "bsp_mat_send": (C.c_int, [_VP, _VP, _VP, C.c_int]),
+    "bsp_mat_recv": (C.c_int, [_VP, _VP, C.c_int, C.POINTER(_VP)]),
+    "bsp_mat_bcast": (C.c_int, [_VP, _VP, C.c_int, _VP, C.POINTER(_VP)]),
+    "bsp_gather_panels": (C.c_int, [_VP, _VP, _VP, C.c_int, C.POINTER(_VP)]),
+    "bsp_chain_distributed": (C.c_int, [_VP, _VP, C.POINTER(_VP), C.c_int32, C.c_int32, C.POINTER(_VP), C.POINTER(Stats),
+                                        C.c_char_p, C.c_size_t]),
+    "bsp_panel_bounds": (C.c_int, [_VP, _VP, _VP, C.c_int32, C.POINTER(C.c_int32)]),
     "bsp_mat_write_bin": (C.c_int, [_VP, _VP, C.c_char_p]),
     "bsp_mat_read_bin": (C.c_int, [_VP, C.c_char_p, C.POINTER(_VP)]),
 }
@@ -180,6 +194,82 @@ class Matrix:
         v = C.c_uint64()
         self.ctx._ck(self.ctx.lib.bsp_mat_checksum(self.ctx.handle, self.handle, C.byref(v)))
         return v.value
+
+    def checksum_body(self):
+        """Order-independent tile sum of this matrix / row panel (add the panels' sums mod 2^64, then
+        checksum_finish with the header of the whole matrix)."""
+        v = C.c_uint64()
+        self.ctx._ck(self.ctx.lib.bsp_mat_checksum_body(self.ctx.handle, self.handle, C.byref(v)))
+        return v.value
+
+
+def checksum_finish(rows, cols, k, esize, nnzb, body):
+    return load_library().bsp_checksum_finish(rows, cols, k, esize, nnzb, body & 0xFFFFFFFFFFFFFFFF)
+
+
+COMM_ID_BYTES = 128
+
+
+def comm_unique_id():
+    """Rendezvous token for Comm (made by one rank, handed to the others by any means)."""
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    if load_library().bsp_comm_unique_id(buf, COMM_ID_BYTES) != BSP_OK:
+        raise BspError(2, "bsp_comm_unique_id failed (NCCL not available?)")
+    return buf.raw
+
+
+class Comm:
+    """One NCCL communicator of the C ABI (replaces MPI_COMM_WORLD of cu:404-408): collective constructor."""
+
+    def __init__(self, ctx, unique_id, nranks, rank):
+        self.ctx = ctx
+        h = _VP()
+        ctx._ck(ctx.lib.bsp_comm_create(ctx.handle, unique_id, nranks, rank, C.byref(h)))
+        self.handle = h.value
+        self.nranks, self.rank = nranks, rank
+
+    def close(self):
+        if self.handle and self.ctx.handle:
+            self.ctx.lib.bsp_comm_destroy(self.ctx.handle, self.handle)
+        self.handle = None
+
+    @property
+    def bytes_sent(self):
+        v = C.c_int64()
+        self.ctx._ck(self.ctx.lib.bsp_comm_info(self.handle, None, None, C.byref(v)))
+        return v.value
+
+    def send(self, mat, peer):
+        self.ctx._ck(self.ctx.lib.bsp_mat_send(self.ctx.handle, self.handle, mat.handle, peer))
+
+    def recv(self, peer):
+        h = _VP()
+        self.ctx._ck(self.ctx.lib.bsp_mat_recv(self.ctx.handle, self.handle, peer, C.byref(h)))
+        return Matrix(self.ctx, h.value)
+
+    def bcast(self, mat, root):
+        """Returns the root's matrix on every rank (the root gets its own object back)."""
+        h = _VP()
+        self.ctx._ck(self.ctx.lib.bsp_mat_bcast(self.ctx.handle, self.handle, root, mat.handle if mat is not None else None,
+                                                C.byref(h)))
+        return mat if self.rank == root else Matrix(self.ctx, h.value)
+
+    def gather_panels(self, panel, root=0):
+        h = _VP()
+        self.ctx._ck(self.ctx.lib.bsp_gather_panels(self.ctx.handle, self.handle, panel.handle, root, C.byref(h)))
+        return Matrix(self.ctx, h.value) if self.rank == root else None
+
+    def chain(self, arr, stats=None, log_base=0, want_log=False):
+        """The multi-rank chain of main (cu:438-571): `arr` is THIS rank's sub-chain. Result on rank 0."""
+        n = len(arr)
+        hs = (_VP * max(n, 1))(*[m.handle for m in arr])
+        h = _VP()
+        st = stats if stats is not None else Stats()
+        buf = C.create_string_buffer(64 * max(n, 1) + 64) if want_log else None
+        self.ctx._ck(self.ctx.lib.bsp_chain_distributed(self.ctx.handle, self.handle, hs, n, log_base, C.byref(h), C.byref(st),
+                                                        buf, len(buf) if buf else 0))
+        out = Matrix(self.ctx, h.value) if h.value else None
+        return (out, buf.value.decode()) if want_log else out
 
 
 class Context:
@@ -308,6 +398,12 @@ class Context:
         h = _VP()
         self._ck(self.lib.bsp_mat_concat_panels(self.handle, hs, n, C.byref(h)))
         return Matrix(self, h.value)
+
+    def panel_bounds(self, a, b, nparts):
+        """Row-panel bounds of a*b for nparts GPUs, balanced by tile products per block row (device-side)."""
+        out = (C.c_int32 * (nparts + 1))()
+        self._ck(self.lib.bsp_panel_bounds(self.handle, a.handle, b.handle, nparts, out))
+        return list(out)
 
     def prune_zero_noalloc(self, k, nbrows, nnzb, d_rowptr, d_colidx, d_vals, d_rowptr_out, d_colidx_out, d_vals_out):
         """Zero-tile compaction that allocates nothing (raw device addresses in and out; the

@@ -78,16 +78,21 @@ checksum_kernel(const uint32_t *__restrict__ vals, const int32_t *__restrict__ b
 
 } // namespace
 
-extern "C" int bsp_mat_checksum(bsp_ctx *ctx, const bsp_mat *m, uint64_t *out)
+extern "C" uint64_t bsp_checksum_finish(int32_t rows, int32_t cols, int32_t k, int32_t esize, int64_t nnzb, uint64_t body)
+{
+    uint64_t header = splitmix64((uint64_t)(uint32_t)rows);
+    header = splitmix64(header ^ (uint64_t)(uint32_t)cols);
+    header = splitmix64(header ^ (uint64_t)(uint32_t)k);
+    header = splitmix64(header ^ (uint64_t)(uint32_t)esize);
+    header = splitmix64(header ^ (uint64_t)nnzb);
+    return splitmix64(body ^ header);
+}
+
+extern "C" int bsp_mat_checksum_body(bsp_ctx *ctx, const bsp_mat *m, uint64_t *out)
 {
     if (!ctx || !m || !out) return BSP_ERR_ARG;
     if (m->device != ctx->device) BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_mat_checksum: matrix lives on device %d, context on %d", m->device, ctx->device);
     BSP_CUDA(ctx, cudaSetDevice(ctx->device));
-    uint64_t header = splitmix64((uint64_t)(uint32_t)m->rows);
-    header = splitmix64(header ^ (uint64_t)(uint32_t)m->cols);
-    header = splitmix64(header ^ (uint64_t)(uint32_t)m->k);
-    header = splitmix64(header ^ (uint64_t)(uint32_t)m->esize);
-    header = splitmix64(header ^ (uint64_t)m->nnzb);
     uint64_t body = 0;
     if (m->nnzb > 0) {
         const uint32_t W = (uint32_t)(m->k * m->k * (m->esize / 4));
@@ -118,6 +123,15 @@ extern "C" int bsp_mat_checksum(bsp_ctx *ctx, const bsp_mat *m, uint64_t *out)
         BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         body = *h;
     }
-    *out = splitmix64(body ^ header);
+    *out = body;
+    return BSP_OK;
+}
+
+extern "C" int bsp_mat_checksum(bsp_ctx *ctx, const bsp_mat *m, uint64_t *out)
+{
+    if (!ctx || !m || !out) return BSP_ERR_ARG;
+    uint64_t body = 0;
+    BSP_TRY(bsp_mat_checksum_body(ctx, m, &body));
+    *out = bsp_checksum_finish(m->rows, m->cols, m->k, m->esize, m->nnzb, body);
     return BSP_OK;
 }

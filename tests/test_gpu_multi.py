@@ -106,3 +106,147 @@ def test_nccl_tree_merge_two_ranks(mode):
         want = orc.chain(mats, ranks=2)[0].prune_zero()
         want.write(os.path.join(d, "want"))
         assert open(out, "rb").read() == open(os.path.join(d, "want"), "rb").read()
+
+
+# ---- the C-ABI transport and the distributed chain (csrc/bsp_dist.cu) ------------------------------
+CAPI_WORKER = r'''
+import os, sys
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[2])
+import numpy as np, torch, torch.distributed as dist
+import bsp_dist, bsp_gen, bspgemm
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+ctx = bspgemm.Context(rank)   # its own stream: nothing here depends on torch's
+tok = torch.zeros(bspgemm.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
+if rank == 0:
+    tok.copy_(torch.frombuffer(bytearray(bspgemm.comm_unique_id()), dtype=torch.uint8))
+dist.broadcast(tok, 0)
+torch.cuda.synchronize()
+comm = bspgemm.Comm(ctx, tok.cpu().numpy().tobytes(), world, rank)
+mode, out = sys.argv[4], sys.argv[3]
+if mode == "chain":
+    k, G, n = 4, 40, int(sys.argv[5])
+    parts = bsp_dist.split_chain(n, world)
+    s, e = parts[rank] if rank < len(parts) else (0, -1)
+    mats = [ctx.matrix_from_coo(*bsp_gen.random_matrix(G * k, G * k, k, 0.08, 8100 + i, "edgy")) for i in range(s, e + 1)]
+    for rep in range(2):   # twice: the second run reuses the pool and the NCCL channels
+        res, log = comm.chain(mats, want_log=True, log_base=s)
+        if rank == 0:
+            assert res is not None
+            res.prune_zero().write_text(out)
+        else:
+            assert res is None
+    assert comm.bytes_sent > 0 or world == 1 or n < world
+elif mode == "transport":
+    k, G = 8, 24
+    m = bsp_gen.random_matrix(G * k, G * k, k, 0.1, 4242, "edgy")
+    f = (G * k, G * k, k, m[3], m[4], (bsp_gen.splitmix64(7, m[3].size * k * k).astype(np.float64) / 2.0 ** 64).astype(np.float32))
+    if rank == 0:
+        A = ctx.matrix_from_coo(*m)
+        F = ctx.matrix_from_coo_f32(*f)
+        comm.send(A, 1)
+        comm.send(F, 1)          # float32 tiles travel through the same calls (SURVEY 8e row 3)
+        back = comm.recv(1)
+        assert back.checksum() == A.checksum()
+        assert comm.bcast(A, 0) is A
+        Fb = comm.bcast(None, 1)
+        assert Fb.is_f32 and Fb.checksum() == F.checksum()
+    elif rank == 1:
+        A = comm.recv(0)
+        F = comm.recv(0)
+        assert F.is_f32 and not A.is_f32
+        br, bc, v = A.to_coo()
+        assert np.array_equal(br, m[3]) and np.array_equal(bc, m[4]) and np.array_equal(v.reshape(-1), m[5].reshape(-1))
+        _, _, fv = F.to_coo()
+        assert np.array_equal(fv.reshape(-1), f[5].reshape(-1))
+        comm.send(A, 0)
+        A2 = comm.bcast(None, 0)
+        assert A2.checksum() == A.checksum()
+        comm.bcast(F, 1)
+    else:
+        A2 = comm.bcast(None, 0)
+        F2 = comm.bcast(None, 1)
+        assert F2.is_f32
+    # row panels of one product, float32 and uint64, gathered on rank 0 = the whole product
+    for mk in ("u64", "f32"):
+        X = ctx.matrix_from_coo(*m) if mk == "u64" else ctx.matrix_from_coo_f32(*f)
+        bounds = ctx.panel_bounds(X, X, world)
+        assert bounds[0] == 0 and bounds[-1] == G and all(bounds[i] <= bounds[i + 1] for i in range(world))
+        P = ctx.helper(X, X, panel=(bounds[rank], bounds[rank + 1]))
+        full = comm.gather_panels(P, 0)
+        if rank == 0:
+            whole = ctx.helper(X, X)
+            assert full.checksum() == whole.checksum(), mk
+            a, b, c = full.to_coo(); a2, b2, c2 = whole.to_coo()
+            assert np.array_equal(a, a2) and np.array_equal(b, b2) and np.array_equal(c, c2)
+        else:
+            assert full is None
+    if rank == 0:
+        open(out, "w").write("ok")
+dist.barrier()
+comm.close()
+dist.destroy_process_group()
+'''
+
+
+def _run_capi(world, args, port):
+    pkg = os.path.dirname(bspgemm.__file__)
+    with tempfile.TemporaryDirectory() as d:
+        script = os.path.join(d, "w.py")
+        open(script, "w").write(CAPI_WORKER)
+        out = os.path.join(d, "matrix")
+        p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world,
+                            "--master-addr", "127.0.0.1", "--master-port", str(port), script, pkg,
+                            os.path.join(util.ROOT, "oracle"), out] + args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+        assert p.returncode == 0, p.stderr.decode()[-3000:]
+        return open(out, "rb").read()
+
+
+@pytest.mark.parametrize("world,n", [(2, 9), (2, 1), (3, 7), (4, 9), (8, 19), (8, 5)])
+def test_capi_chain_distributed_matches_rank_tree(world, n):
+    """bsp_chain_distributed over NCCL against the oracle's P-rank tree (cu:438-456 + cu:569-571), byte for
+    byte through the writer; n < world exercises the 'only rank 0 works' rule (cu:612-616)."""
+    if _ngpu() < world:
+        pytest.skip("needs %d GPUs" % world)
+    k, G = 4, 40
+    got = _run_capi(world, ["chain", str(n)], 29621 + world)
+    mats = [orc.OMat.from_coo(*bsp_gen.random_matrix(G * k, G * k, k, 0.08, 8100 + i, "edgy")) for i in range(n)]
+    with tempfile.TemporaryDirectory() as d:
+        orc.chain(mats, ranks=world)[0].prune_zero().write(os.path.join(d, "want"))
+        assert got == open(os.path.join(d, "want"), "rb").read()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_capi_transport_send_recv_bcast_gather(world):
+    if _ngpu() < world:
+        pytest.skip("needs %d GPUs" % world)
+    assert _run_capi(world, ["transport"], 29641 + world) == b"ok"
+
+
+def test_capi_comm_single_rank():
+    """One rank: the communicator degenerates to the local chain (runs on the 1-GPU test box)."""
+    import ctypes
+    k, G, n = 4, 30, 5
+    with bspgemm.Context(0) as ctx:
+        comm = bspgemm.Comm(ctx, bspgemm.comm_unique_id(), 1, 0)
+        host = [bsp_gen.random_matrix(G * k, G * k, k, 0.1, 9100 + i, "edgy") for i in range(n)]
+        mats = [ctx.matrix_from_coo(*m) for m in host]
+        res = comm.chain(mats)
+        want = ctx.helper2(mats)
+        assert res.checksum() == want.checksum()
+        A = mats[0]
+        assert ctx.panel_bounds(A, mats[1], 1) == [0, A.device_view()[0]]
+        b4 = ctx.panel_bounds(A, mats[1], 4)
+        assert b4[0] == 0 and b4[4] == A.device_view()[0] and b4 == sorted(b4)
+        # panels by those bounds add up to the whole product, also by checksum parts
+        whole = ctx.helper(A, mats[1])
+        body, nn = 0, 0
+        for i in range(4):
+            P = ctx.helper(A, mats[1], panel=(b4[i], b4[i + 1]))
+            body = (body + P.checksum_body()) & 0xFFFFFFFFFFFFFFFF
+            nn += P.nnzb
+        r, c, kk, _ = whole.info()
+        assert bspgemm.checksum_finish(r, c, kk, 8, nn, body) == whole.checksum()
+        assert comm.gather_panels(whole, 0).checksum() == whole.checksum()
+        comm.close()
