@@ -191,6 +191,31 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
+// The multiply-add with the 64-bit accumulator SPLIT: s collects the low x low partial products (one
+// IMAD.WIDE.U32 with the accumulator as addend) and a separate 32-bit x collects the two cross terms (two
+// IMAD with x as addend); the true value is s + (x << 32), formed once per output tile.  nvcc's own
+// lowering of s += a*b (MACV = 0, mac_flag) needs a fourth instruction per step, the add of the cross
+// terms into the high word, which ptxas often issues as IMAD.IADD on the multiplier pipe.  The detector
+// only looks at low words, which x never touches, so it is unchanged.  The low product is spelled
+// mul.wide.u32 in PTX: written as C++ 64-bit arithmetic nvcc emits a 64 x 64 multiply of zero-extended
+// values and ptxas leaves additions of zero behind; written as mad.wide.u32 ptxas splits the accumulate
+// into IMAD.WIDE + IADD3 + IADD3.X.  configs[1]: 7.68 -> 6.82 warp instructions per warp-MAC, 11.47 ->
+// 11.01 ms under ncu; the chain's k=4 top product 5.83 -> 5.36 ms.
+template <int MACV>
+__device__ __forceinline__ void mac_split(uint64_t &s, uint32_t &x, uint32_t &flag, uint64_t a, uint64_t b)
+{
+    if (MACV == 0) { mac_flag(s, flag, a, b); return; }
+    const uint32_t al = (uint32_t)a, ah = (uint32_t)(a >> 32), bl = (uint32_t)b, bh = (uint32_t)(b >> 32);
+    const uint32_t lo_old = (uint32_t)s;
+    uint64_t t;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(t) : "r"(al), "r"(bl));
+    s += t;
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(x) : "r"(al), "r"(bh));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(x) : "r"(ah), "r"(bl));
+    const uint32_t lo = (uint32_t)s;
+    flag = max(flag, max(lo, lo - lo_old));
+}
+
 // A group of TPT threads owns one output tile at a time; thread h of the group holds rows
 // h, h+TPT, ... (RPT = K/TPT rows, K accumulators each).  Fewer threads per tile means fewer
 // redundant shared-memory reads of the B tile (every thread of a group needs all of it): the
@@ -236,8 +261,8 @@ __device__ __forceinline__ ulonglong2 lds128(unsigned smem_addr)
     return v;
 }
 
-template <int K, int STAGES, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, (WARPS == 4 && K == 4) ? 3 : 1)
+template <int K, int STAGES, int WARPS, int MINB, int MACV>
+__global__ void __launch_bounds__(WARPS * 32, MINB)
 numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restrict__ b_vals,
                     const int64_t *__restrict__ pair_ptr, const int2 *__restrict__ pairs,
                     const int2 *__restrict__ chunk_tiles, const int32_t *__restrict__ nchunks_ptr,
@@ -326,11 +351,12 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
     }
 
     uint64_t acc[RPT][K];
+    uint32_t xs[RPT][K]; // cross-term sums of the split form (MACV != 0), else unused
     uint32_t flag = 0;
 #pragma unroll
     for (int rr = 0; rr < RPT; rr++)
 #pragma unroll
-        for (int c = 0; c < K; c++) acc[rr][c] = 0;
+        for (int c = 0; c < K; c++) { acc[rr][c] = 0; xs[rr][c] = 0; }
 
     // per-thread read addresses inside a stage: two A rows (swizzled chunks) and the B tile
     const unsigned gbase = wbase + grp * Cfg::GROUP_STRIDE;
@@ -386,12 +412,18 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
                 for (int c2 = 0; c2 < K / 2; c2++) {
 #pragma unroll
                     for (int rr = 0; rr < RPT; rr++) {
-                        mac_flag(acc[rr][2 * c2], flag, a_cur[rr][j], bcur[c2].x);
-                        mac_flag(acc[rr][2 * c2 + 1], flag, a_cur[rr][j], bcur[c2].y);
+                        mac_split<MACV>(acc[rr][2 * c2], xs[rr][2 * c2], flag, a_cur[rr][j], bcur[c2].x);
+                        mac_split<MACV>(acc[rr][2 * c2 + 1], xs[rr][2 * c2 + 1], flag, a_cur[rr][j], bcur[c2].y);
                     }
                 }
             }
             if (lastq & 1u) { // last pair of the tile: write this thread's rows, move on
+                if (MACV != 0) {
+#pragma unroll
+                    for (int rr = 0; rr < RPT; rr++)
+#pragma unroll
+                        for (int c = 0; c < K; c++) acc[rr][c] += (uint64_t)xs[rr][c] << 32;
+                }
                 if (flag == 0xffffffffu) {
                     const int64_t p0 = pair_ptr[t], p1 = (prs - pairs) + k + 1;
 #pragma unroll
@@ -411,7 +443,7 @@ numeric_rows_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restr
                     for (int i = 0; i < K / 2; i++)
                         __stcs(&out[i], make_ulonglong2(acc[rr][2 * i], acc[rr][2 * i + 1]));
 #pragma unroll
-                    for (int c = 0; c < K; c++) acc[rr][c] = 0;
+                    for (int c = 0; c < K; c++) { acc[rr][c] = 0; xs[rr][c] = 0; }
                 }
                 flag = 0;
                 t++;
@@ -441,7 +473,7 @@ struct BigCfg {
     static constexpr int STAGE_BYTES = GROUPS * TILE_BYTES;
 };
 
-template <int K, int WARPS>
+template <int K, int WARPS, int MACV>
 __global__ void __launch_bounds__(WARPS * 32)
 numeric_bigtile_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__restrict__ b_vals,
                        const int64_t *__restrict__ pair_ptr, const int2 *__restrict__ pairs,
@@ -494,9 +526,10 @@ numeric_bigtile_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__re
     cp_async_commit();
 
     uint64_t acc[K];
+    uint32_t xs[K]; // cross-term sums of the split multiply-add (mac_split)
     uint32_t flag = 0;
 #pragma unroll
-    for (int c = 0; c < K; c++) acc[c] = 0;
+    for (int c = 0; c < K; c++) { acc[c] = 0; xs[c] = 0; }
 
     for (int k = 0; k < steps; k++) {
         cp_async_wait<0>();
@@ -523,12 +556,16 @@ numeric_bigtile_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__re
 #pragma unroll
                     for (int c2 = 0; c2 < K / 2; c2++) {
                         const ulonglong2 bv = lds128(bsm + (j * (K / 2) + c2) * 16); // broadcast inside the group
-                        mac_flag(acc[2 * c2], flag, a, bv.x);
-                        mac_flag(acc[2 * c2 + 1], flag, a, bv.y);
+                        mac_split<MACV>(acc[2 * c2], xs[2 * c2], flag, a, bv.x);
+                        mac_split<MACV>(acc[2 * c2 + 1], xs[2 * c2 + 1], flag, a, bv.y);
                     }
                 }
             }
             if (cur.y < 0) { // last pair of the tile
+                if (MACV != 0) {
+#pragma unroll
+                    for (int c = 0; c < K; c++) acc[c] += (uint64_t)xs[c] << 32;
+                }
                 if (flag == 0xffffffffu) {
                     uint64_t exact[K];
                     refold_row_exact<K>(a_vals, b_vals, pairs, pair_ptr[t], (prs - pairs) + k + 1, r, exact);
@@ -540,7 +577,7 @@ numeric_bigtile_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__re
 #pragma unroll
                 for (int i = 0; i < K / 2; i++) __stcs(&out[i], make_ulonglong2(acc[2 * i], acc[2 * i + 1]));
 #pragma unroll
-                for (int c = 0; c < K; c++) acc[c] = 0;
+                for (int c = 0; c < K; c++) { acc[c] = 0; xs[c] = 0; }
                 flag = 0;
                 t++;
             }
@@ -551,13 +588,14 @@ numeric_bigtile_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__re
     cp_async_wait<0>();
 }
 
-struct NumericTuning { int Q; int panel_mb; int stages; int warps; bool q_forced; };
+struct NumericTuning { int Q; int panel_mb; int stages; int warps; bool q_forced; int macv; };
 
 NumericTuning numeric_tuning()
 {
-    NumericTuning tn = {96, 1 << 20, 2, 4, false}; // panels off by default: measured no gain on cfg2 (see profiles/)
+    NumericTuning tn = {96, 1 << 20, 2, 4, false, 3}; // panels off by default: measured no gain on cfg2 (see profiles/)
     if (const char *e = getenv("BSP_NUM_Q")) { int v = atoi(e); if (v >= 1) { tn.Q = v; tn.q_forced = true; } }
     if (const char *e = getenv("BSP_NUM_PANEL_MB")) { int v = atoi(e); if (v >= 1) tn.panel_mb = v; }
+    if (const char *e = getenv("BSP_NUM_MACV")) tn.macv = atoi(e) == 0 ? 0 : 3; // 0: the first kernel's plain 64-bit form
     if (const char *e = getenv("BSP_NUM_WARPS")) { int v = atoi(e); if (v == 4 || v == 8) tn.warps = v; }
     return tn;
 }
@@ -613,7 +651,7 @@ void release_schedule(bsp_ctx *ctx, ChunkSchedule *cs)
     bsp_release(ctx, cs->seg_ts); bsp_release(ctx, cs->seg_nch); bsp_release(ctx, cs->seg_off); bsp_release(ctx, cs->chunk_tiles);
 }
 
-template <int K, int STAGES, int WARPS>
+template <int K, int STAGES, int WARPS, int MINB, int MACV>
 int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symbolic_out *sym, int nbr,
                     const int32_t *c_rowptr, uint64_t *c_vals, const NumericTuning &tn)
 {
@@ -622,7 +660,7 @@ int launch_rows_cfg(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_
     ChunkSchedule cs;
     BSP_TRY(build_schedule(ctx, B, sym, nbr, c_rowptr, Cfg::TILE_BYTES, tn, &cs));
     const size_t smem = (size_t)WARPS * Cfg::WARP_BYTES(STAGES);
-    auto kern = numeric_rows_kernel<K, STAGES, WARPS>;
+    auto kern = numeric_rows_kernel<K, STAGES, WARPS, MINB, MACV>;
     BSP_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = (cs.max_chunks + groups_per_cta - 1) / groups_per_cta;
     kern<<<grid, WARPS * 32, smem, ctx->stream>>>(A->vals, B->vals, sym->pair_ptr, sym->pairs, cs.chunk_tiles,
@@ -642,7 +680,7 @@ int launch_bigtile(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_s
     ChunkSchedule cs;
     BSP_TRY(build_schedule(ctx, B, sym, nbr, c_rowptr, Cfg::TILE_BYTES, tn, &cs));
     const size_t smem = (size_t)WARPS * 2 * Cfg::STAGE_BYTES;
-    auto kern = numeric_bigtile_kernel<K, WARPS>;
+    auto kern = tn.macv == 0 ? numeric_bigtile_kernel<K, WARPS, 0> : numeric_bigtile_kernel<K, WARPS, 3>;
     BSP_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int groups_per_cta = WARPS * Cfg::GROUPS;
     const int grid = (cs.max_chunks + groups_per_cta - 1) / groups_per_cta;
@@ -658,10 +696,11 @@ int launch_rows(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
                 const int32_t *c_rowptr, uint64_t *c_vals)
 {
     const NumericTuning tn = numeric_tuning();
-#ifdef BSP_TUNING_VARIANTS // one more instantiation per tile size, measured no faster
-    if (tn.warps == 8) return launch_rows_cfg<K, 2, 8>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
-#endif
-    return launch_rows_cfg<K, 2, 4>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
+    // resident CTAs per SM the register allocation aims at: 3 (12 warps).  Measured on configs[1]: a 4-CTA build
+    // (126 registers) runs 16 % slower, the kernel is bound by integer instruction issue, not by latency.
+    constexpr int MINB = K == 8 ? 1 : 3;
+    if (tn.macv == 0) return launch_rows_cfg<K, 2, 4, MINB, 0>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
+    return launch_rows_cfg<K, 2, 4, MINB, 3>(ctx, A, B, sym, nbr, c_rowptr, c_vals, tn);
 }
 
 } // namespace

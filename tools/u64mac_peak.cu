@@ -4,6 +4,9 @@
 //   plain   : s += a*b                      (wrapping; what a flag-free fast path would cost)
 //   flagged : plain + conservative 2^64-1 detector on the low words (the shipped fast path)
 //   exact   : phi after the multiply and after the add (the reference's per-op arithmetic)
+//   split   : flagged, with the low x low products in the 64-bit accumulator (IMAD.WIDE) and the cross terms in
+//             a separate 32-bit accumulator (two IMAD), i.e. without the add into the high word
+//   splitp  : split without the detector
 // Each thread keeps 8 accumulators (one output row of a k=8 tile), A row in registers, B tile
 // read from shared memory with 128-bit broadcast loads -- the inner loop of the real kernel
 // without its global loads.
@@ -21,9 +24,11 @@ __global__ void __launch_bounds__(256) mac_kernel(const uint64_t *__restrict__ s
     for (int i = threadIdx.x; i < 512; i += 256) tile[i >> 6][i & 63] = src[i] | 1;
     __syncthreads();
     uint64_t a[8], acc[8];
+    uint32_t xs[8];
 #pragma unroll
-    for (int j = 0; j < 8; j++) { a[j] = src[(threadIdx.x * 8 + j) & 511] + blockIdx.x; acc[j] = 0; }
-    uint32_t flag = 0;
+    for (int j = 0; j < 8; j++) { a[j] = src[(threadIdx.x * 8 + j) & 511] + blockIdx.x; acc[j] = 0; xs[j] = 0; }
+    uint32_t flag = MODE == 8 ? 0xffffffffu : 0, flag2 = MODE >= 7 ? 0xffffffffu : 0;
+    bool hit = false;
     for (int it = 0; it < iters; it++) {
         const uint64_t *B = tile[it & 7];
 #pragma unroll
@@ -41,18 +46,34 @@ __global__ void __launch_bounds__(256) mac_kernel(const uint64_t *__restrict__ s
                         acc[c + h] += a[j] * bb[h];
                         const uint32_t lo = (uint32_t)acc[c + h];
                         flag = max(flag, max(lo, lo - lo_old));
-                    } else {
+                    } else if (MODE == 2) {
                         acc[c + h] = phi(acc[c + h] + phi(a[j] * bb[h]));
+                    } else {
+                        const uint32_t al = (uint32_t)a[j], ah = (uint32_t)(a[j] >> 32), bl = (uint32_t)bb[h], bh = (uint32_t)(bb[h] >> 32);
+                        const uint32_t lo_old = (uint32_t)acc[c + h];
+                        uint64_t t;
+                        asm("mul.wide.u32 %0, %1, %2;" : "=l"(t) : "r"(al), "r"(bl));
+                        acc[c + h] += t;
+                        asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(xs[c + h]) : "r"(al), "r"(bh));
+                        asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(xs[c + h]) : "r"(ah), "r"(bl));
+                        const uint32_t lo = (uint32_t)acc[c + h];
+                        if (MODE == 3) flag = max(flag, max(lo, lo - lo_old));
+                        if (MODE == 5) hit = hit | (lo == 0xffffffffu) | (lo_old - lo == 1u);          // compare + predicate OR
+                        if (MODE == 6) { flag = max(flag, lo); flag2 = max(flag2, lo - lo_old); }     // two-input max only
+                        if (MODE == 7) { flag |= ~lo - 1u < 0x7fffffffu ? 0u : 0u; flag2 = min(flag2, min(~lo, lo_old + ~lo)); } // min3 form
+                        if (MODE == 8) { flag = min(flag, ~lo); flag2 = min(flag2, lo_old + ~lo); }   // two-input min of "distance to the event"
                     }
                 }
             }
         }
+        // fresh A values every iteration, as in the real kernel (and nothing the compiler can strength-reduce)
+        const ulonglong2 *an = reinterpret_cast<const ulonglong2 *>(&tile[(it + 3) & 7][(threadIdx.x & 7) * 8]);
 #pragma unroll
-        for (int j = 0; j < 8; j++) a[j] += 2; // keep the loop body from being hoisted
+        for (int j = 0; j < 8; j += 2) { const ulonglong2 v = an[j / 2]; a[j] = v.x; a[j + 1] = v.y; }
     }
-    uint64_t r = flag;
+    uint64_t r = flag + flag2 + (hit ? 12345u : 0u);
 #pragma unroll
-    for (int j = 0; j < 8; j++) r ^= acc[j];
+    for (int j = 0; j < 8; j++) r ^= acc[j] + ((uint64_t)xs[j] << 32);
     out[blockIdx.x * 256 + threadIdx.x] = r;
 }
 
@@ -88,10 +109,15 @@ int main()
     for (int i = 0; i < 512; i++) { z ^= z << 13; z ^= z >> 7; z ^= z << 17; h[i] = z; }
     cudaMemcpy(src, h, sizeof h, cudaMemcpyHostToDevice);
     printf("{\"device\": \"%s\", \"sms\": %d, \"clock_khz\": %d}\n", p.name, sms, p.clockRate);
-    for (int occ = 2; occ <= 8; occ *= 2) {
+    for (int occ = 4; occ <= 4; occ *= 2) {
         run<0>("plain", sms * occ, 2000, src, out);
         run<1>("flagged", sms * occ, 2000, src, out);
         run<2>("exact", sms * occ, 2000, src, out);
+        run<3>("split", sms * occ, 2000, src, out);
+        run<4>("splitp", sms * occ, 2000, src, out);
+        run<5>("split_setp", sms * occ, 2000, src, out);
+        run<6>("split_max2", sms * occ, 2000, src, out);
+        run<8>("split_min2", sms * occ, 2000, src, out);
     }
     return 0;
 }
