@@ -316,6 +316,25 @@ def test_symbolic_row_classes_and_generic_numeric(ctx):
         os.environ.pop("BSP_FORCE_GENERIC", None)
 
 
+@pytest.mark.parametrize("k,G,da,db,kind", [(4, 160, 0.15, 0.2, "edgy"), (8, 700, 0.05, 0.05, "u64"), (4, 300, 0.4, 0.5, "edgy"),
+                                              (2, 2100, 0.02, 0.03, "edgy")])
+def test_symbolic_medium_rows_against_oracle(ctx, k, G, da, db, kind):
+    """Rows of a few hundred to a few thousand tile products (the shared-memory fill classes at the sizes
+    of a single large product): B rows longer than a warp, many pairs per tile, and the 2^64-1 edge
+    values whose fold order would expose a mis-ordered pair list; with and without the bit-matrix fill."""
+    import os
+    a = bsp_gen.random_matrix(G * k, G * k, k, da, 181, kind)
+    b = bsp_gen.random_matrix(G * k, G * k, k, db, 182, kind)
+    ref = orc.multiply(orc.OMat.from_coo(*a), orc.OMat.from_coo(*b))[0]
+    try:
+        got = ctx.helper(dev(ctx, a), dev(ctx, b))
+        assert_same(got, ref)
+        os.environ["BSP_SYM_NO_DENSE"] = "1"
+        assert ctx.helper(dev(ctx, a), dev(ctx, b)).checksum() == got.checksum()
+    finally:
+        os.environ.pop("BSP_SYM_NO_DENSE", None)
+
+
 def test_concat_panels(ctx):
     k, G = 4, 120
     a = bsp_gen.random_matrix(G * k, G * k, k, 0.06, 91, "edgy")
