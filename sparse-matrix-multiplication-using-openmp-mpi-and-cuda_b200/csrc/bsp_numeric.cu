@@ -149,10 +149,21 @@ __global__ void seg_bounds_kernel(int nbr, int npanels, int panel_w, const int32
     seg_nchunks[x] = (int)((np + Q - 1) / Q);
 }
 
+// logarithmic size class of a chunk of n tile products: 8 classes per octave, 0 for an empty chunk
+__device__ __forceinline__ unsigned char chunk_bucket(int64_t n)
+{
+    if (n <= 0) return 0;
+    if (n >= ((int64_t)1 << 31)) return 255;
+    const unsigned v = (unsigned)n;
+    const int l = 31 - __clz(v);
+    const int sub = l >= 3 ? (int)((v >> (l - 3)) & 7u) : 0;
+    return (unsigned char)min(255, l * 8 + sub + 1);
+}
+
 __global__ void chunk_fill_kernel(int nbr, int npanels, int panel_w, const int32_t *__restrict__ c_rowptr,
                                   const int32_t *__restrict__ c_colidx, const int64_t *__restrict__ pair_ptr, int Q,
                                   const int32_t *__restrict__ seg_ts, const int32_t *__restrict__ seg_off,
-                                  int2 *__restrict__ chunk_tiles)
+                                  int2 *__restrict__ chunk_tiles, unsigned char *__restrict__ chunk_key)
 {
     const int nseg = nbr * npanels;
     const int total = seg_off[nseg];
@@ -173,7 +184,67 @@ __global__ void chunk_fill_kernel(int nbr, int npanels, int panel_w, const int32
     const int t0 = l == 0 ? ts : lower_bound_i64(pair_ptr, ts, te, base + (int64_t)l * Q);
     const int t1 = l == n - 1 ? te : lower_bound_i64(pair_ptr, ts, te, base + (int64_t)(l + 1) * Q);
     chunk_tiles[x] = make_int2(t0, t1);
+    if (chunk_key) chunk_key[x] = chunk_bucket(pair_ptr[t1] - pair_ptr[t0]);
 }
+
+// -- chunks ordered by size ---------------------------------------------------------------------
+// The groups of a warp step through their chunks in lockstep, so a warp is as slow as its longest chunk.
+// A chunk is "whole tiles until Q products are reached": with a skewed pattern (R-MAT: 3 % of the products
+// sit in tiles of more than 96 pairs, one tile has 1887) the eight chunks of a warp differ widely and the
+// lockstep wastes 17 % of the lanes' steps over the whole product, 30 % in the hub rows.  The chunks are
+// therefore put in descending order of a logarithmic size class (8 classes per octave) by a counting
+// sort: warps get chunks of nearly equal length (98 % of the steps useful in the same simulation) and the
+// long ones start first.  Inside a class the order of the rows is kept block by block, so chunks of one
+// block row of C still run side by side and share the A tiles in L1/L2.
+constexpr int CHUNK_CLASSES = 256;
+constexpr int CSORT_THREADS = 256;
+
+__global__ void __launch_bounds__(CSORT_THREADS)
+chunk_hist_kernel(const unsigned char *__restrict__ key, const int32_t *__restrict__ total_ptr, int32_t *__restrict__ hist)
+{
+    __shared__ int h[CHUNK_CLASSES];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int x = blockIdx.x * CSORT_THREADS + threadIdx.x;
+    if (x < *total_ptr) atomicAdd(&h[key[x]], 1);
+    __syncthreads();
+    if (h[threadIdx.x]) atomicAdd(&hist[threadIdx.x], h[threadIdx.x]);
+}
+
+__global__ void __launch_bounds__(CSORT_THREADS)
+chunk_scatter_kernel(const unsigned char *__restrict__ key, const int2 *__restrict__ chunk_tiles,
+                     const int32_t *__restrict__ total_ptr, const int32_t *__restrict__ hist, int32_t *__restrict__ cursor,
+                     int2 *__restrict__ sorted)
+{
+    __shared__ int base[CHUNK_CLASSES], cnt[CHUNK_CLASSES], resv[CHUNK_CLASSES];
+    const int tid = threadIdx.x;
+    // first slot of class b in descending class order = chunks in the classes above b
+    {
+        int v = hist[CHUNK_CLASSES - 1 - tid]; // tid-th largest class
+        base[tid] = v;
+        __syncthreads();
+        for (int d = 1; d < CHUNK_CLASSES; d <<= 1) { // inclusive scan over 256 entries
+            const int o = tid >= d ? base[tid - d] : 0;
+            __syncthreads();
+            base[tid] += o;
+            __syncthreads();
+        }
+        const int excl = base[tid] - v;
+        __syncthreads();
+        base[tid] = excl; // indexed by position in descending order: class b sits at CHUNK_CLASSES-1-b
+    }
+    cnt[tid] = 0;
+    __syncthreads();
+    const int x = blockIdx.x * CSORT_THREADS + tid;
+    const bool in = x < *total_ptr;
+    int b = 0, local = 0;
+    if (in) { b = key[x]; local = atomicAdd(&cnt[b], 1); }
+    __syncthreads();
+    if (cnt[tid]) resv[tid] = atomicAdd(&cursor[tid], cnt[tid]);
+    __syncthreads();
+    if (in) sorted[base[CHUNK_CLASSES - 1 - b] + resv[b] + local] = chunk_tiles[x];
+}
+
 
 // -- the kernel -------------------------------------------------------------------------------
 
@@ -588,13 +659,14 @@ numeric_bigtile_kernel(const uint64_t *__restrict__ a_vals, const uint64_t *__re
     cp_async_wait<0>();
 }
 
-struct NumericTuning { int Q; int panel_mb; int stages; int warps; bool q_forced; int macv; };
+struct NumericTuning { int Q; int panel_mb; int stages; int warps; bool q_forced; int macv; bool sort_chunks; };
 
 NumericTuning numeric_tuning()
 {
-    NumericTuning tn = {96, 1 << 20, 2, 4, false, 3}; // panels off by default: measured no gain on cfg2 (see profiles/)
+    NumericTuning tn = {96, 1 << 20, 2, 4, false, 3, true}; // panels off by default: measured no gain on cfg2 (see profiles/)
     if (const char *e = getenv("BSP_NUM_Q")) { int v = atoi(e); if (v >= 1) { tn.Q = v; tn.q_forced = true; } }
     if (const char *e = getenv("BSP_NUM_PANEL_MB")) { int v = atoi(e); if (v >= 1) tn.panel_mb = v; }
+    if (const char *e = getenv("BSP_NUM_SORT")) tn.sort_chunks = atoi(e) != 0; // 0: chunks stay in row order (comparison hook)
     if (const char *e = getenv("BSP_NUM_MACV")) tn.macv = atoi(e) == 0 ? 0 : 3; // 0: the first kernel's plain 64-bit form
     if (const char *e = getenv("BSP_NUM_WARPS")) { int v = atoi(e); if (v == 4 || v == 8) tn.warps = v; }
     return tn;
@@ -638,9 +710,29 @@ int build_schedule(bsp_ctx *ctx, const bsp_mat *B, const bsp_symbolic_out *sym, 
         nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, cs->seg_ts, cs->seg_nch);
     BSP_LAUNCH_CHECK(ctx);
     BSP_TRY(bsp_scan_i32(ctx, cs->seg_nch, cs->seg_off, cs->nseg + 1, nullptr));
+    // panels off (the default): chunks in descending size class; with panels the panel-major order is the point
+    const bool by_size = npanels == 1 && tn.sort_chunks;
+    unsigned char *key = nullptr;
+    int2 *unsorted = nullptr;
+    int32_t *hist = nullptr;
+    if (by_size) {
+        BSP_TRY(sc.alloc(&key, (size_t)cs->max_chunks));
+        BSP_TRY(sc.alloc(&unsorted, (size_t)cs->max_chunks));
+        BSP_TRY(sc.alloc(&hist, (size_t)2 * CHUNK_CLASSES));
+        BSP_CUDA(ctx, cudaMemsetAsync(hist, 0, 2 * CHUNK_CLASSES * sizeof(int32_t), ctx->stream));
+    }
     chunk_fill_kernel<<<(unsigned)((cs->max_chunks + 255) / 256), 256, 0, ctx->stream>>>(
-        nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, cs->seg_ts, cs->seg_off, cs->chunk_tiles);
+        nbr, npanels, panel_w, c_rowptr, sym->c_colidx, sym->pair_ptr, Q, cs->seg_ts, cs->seg_off,
+        by_size ? unsorted : cs->chunk_tiles, key);
     BSP_LAUNCH_CHECK(ctx);
+    if (by_size) {
+        const unsigned g = (unsigned)((cs->max_chunks + CSORT_THREADS - 1) / CSORT_THREADS);
+        chunk_hist_kernel<<<g, CSORT_THREADS, 0, ctx->stream>>>(key, cs->seg_off + cs->nseg, hist);
+        BSP_LAUNCH_CHECK(ctx);
+        chunk_scatter_kernel<<<g, CSORT_THREADS, 0, ctx->stream>>>(key, unsorted, cs->seg_off + cs->nseg, hist, hist + CHUNK_CLASSES,
+                                                                   cs->chunk_tiles);
+        BSP_LAUNCH_CHECK(ctx);
+    }
     bsp_trace_mark(ctx, "num_schedule");
     sc.keep(cs->seg_ts); sc.keep(cs->seg_nch); sc.keep(cs->seg_off); sc.keep(cs->chunk_tiles); // released by release_schedule
     return BSP_OK;

@@ -12,13 +12,13 @@ sys.path.insert(0, os.path.join(ROOT, "sparse-matrix-multiplication-using-openmp
 import bsp_gen  # noqa: E402
 import bspgemm  # noqa: E402
 
-KEYS = ("BSP_NUM_KERNEL", "BSP_NUM_PANEL_MB", "BSP_NUM_Q", "BSP_NUM_WARPS", "BSP_NUM_MINB", "BSP_NUM_MACV")
+KEYS = ("BSP_NUM_KERNEL", "BSP_NUM_PANEL_MB", "BSP_NUM_Q", "BSP_NUM_WARPS", "BSP_NUM_MINB", "BSP_NUM_MACV", "BSP_NUM_SORT")
 
 
 def main():
     args = sys.argv[1:]
     workload = "cfg2"
-    if args and args[0] in ("cfg2", "chaintop", "k16", "k32"):
+    if args and args[0] in ("cfg2", "chaintop", "k16", "k32", "rmat"):
         workload, args = args[0], args[1:]
     specs = args or ["", "BSP_NUM_MINB=4"]
     golden = json.load(open(os.path.join(ROOT, "tests", "golden", "full_size.json")))
@@ -28,6 +28,15 @@ def main():
             want = golden["cfg2"]["checksum"]
             A = ctx.matrix_from_coo(*bsp_gen.random_matrix(n, n, k, d, 1000, "u64"))
             B = ctx.matrix_from_coo(*bsp_gen.random_matrix(n, n, k, d, 1001, "u64"))
+        elif workload == "rmat":  # BASELINE configs[3]: R-MAT scale 15, k=8
+            scale, k = 15, 8
+            G = 1 << scale
+            want = golden["rmat"]["checksum"]
+            ms_ = []
+            for seed in (11, 12):
+                br, bc = bsp_gen.rmat_pattern(scale, 16, seed)
+                ms_.append(ctx.matrix_from_coo(G * k, G * k, k, br, bc, bsp_gen.values(seed, br.size * k * k, "u64").reshape(-1, k, k)))
+            A, B = ms_
         elif workload in ("k16", "k32"):  # bench.py's large-tile u64 workloads; no golden: the variants must agree with each other
             sys.path.insert(0, ROOT)
             import bench
