@@ -13,9 +13,12 @@
 // (N/P each, the last one takes the remainder; fewer matrices than ranks -> one sub-chain),
 // every sub-chain is reduced by the pairwise tree, the P partial products are reduced by the
 // same tree (cu:569-571), and all-zero tiles are dropped from the final product (cu:577-592).
-// Sub-chain r runs on CUDA device r mod D on its own host thread; partial products move
-// device-to-device into device 0, and every large product of the merge is sharded by block rows over
-// the D devices (same tree, same bits).  Default P = 1, D = all visible.
+// Sub-chain r runs on CUDA device r mod D on its own host thread.  With P <= D every rank has a device
+// of its own: the ranks form an NCCL communicator and bsp_chain_distributed reduces the whole chain
+// (ncclSend / ncclRecv over NVLink, every merge product sharded over the ranks of its subtree).  With
+// P > D the partial products move device-to-device into device 0 and every large product of the merge
+// is sharded by block rows over the D devices.  Same tree, same bits either way.  Default P = 1,
+// D = all visible.
 //
 // Additions without a counterpart in the reference (off by default, the default run is the
 // reference's): --binary reads <folder>/matrixI.bin where it exists (else the text file) and
@@ -39,6 +42,7 @@ namespace {
 struct Rank {
     int start = 0, end = -1, device = 0;
     bsp_ctx *ctx = nullptr;
+    bsp_comm *comm = nullptr; // one NCCL rank per device when every sub-chain has a device of its own
     std::vector<bsp_mat *> mats;
     bsp_mat *partial = nullptr;
     std::string log;
@@ -53,10 +57,19 @@ bool file_exists(const std::string &p)
     return f != nullptr;
 }
 
-void run_rank(Rank *r, const std::string &folder, int k, bool binary)
+// nccl_id != nullptr: this thread is NCCL rank `rank` of `nranks` (one device each) and the whole chain is
+// reduced by bsp_chain_distributed, which replaces MPI_Send / MPI_Recv of the partial products and the
+// rank-0 merge (cu:471-571); every rank must reach the collective calls, so a rank that failed to load
+// its files still takes part with an empty sub-chain and reports its error afterwards.
+void run_rank(Rank *r, const std::string &folder, int k, bool binary, const void *nccl_id, int rank, int nranks)
 {
     r->rc = bsp_ctx_create(r->device, nullptr, &r->ctx);
-    if (r->rc) { r->err = r->ctx ? bsp_last_error(r->ctx) : "context"; return; }
+    if (r->rc) { r->err = r->ctx ? bsp_last_error(r->ctx) : "context"; if (!nccl_id) return; }
+    if (nccl_id && r->ctx) {
+        int crc = bsp_comm_create(r->ctx, nccl_id, nranks, rank, &r->comm);
+        if (crc && !r->rc) { r->rc = crc; r->err = bsp_last_error(r->ctx); }
+    }
+    if (r->rc) return;
     const int n = r->end - r->start + 1;
     r->mats.assign((size_t)n, nullptr);
     // The reference parses its files with one OpenMP task each (cu:334-339).  Here the text files of
@@ -82,8 +95,17 @@ void run_rank(Rank *r, const std::string &folder, int k, bool binary)
         if (r->rc) r->err = bsp_last_error(r->ctx);
         else for (size_t j = 0; j < got.size(); j++) r->mats[text_slot[j]] = got[j];
     }
-    if (r->rc) return;
     std::vector<char> log((size_t)n * 64 + 64);
+    if (r->comm) {
+        // collective: a rank whose files failed passes an empty sub-chain so that the others do not hang
+        const int load_rc = r->rc;
+        const int nl = load_rc ? 0 : n;
+        int crc = bsp_chain_distributed(r->ctx, r->comm, r->mats.data(), nl, r->start, &r->partial, nullptr, log.data(), log.size());
+        if (!load_rc && crc) { r->rc = crc; r->err = bsp_last_error(r->ctx); }
+        if (!r->rc) r->log = log.data();
+        return;
+    }
+    if (r->rc) return;
     r->rc = bsp_chain(r->ctx, r->mats.data(), n, &r->partial, nullptr, log.data(), log.size(), r->start);
     if (r->rc) { r->err = bsp_last_error(r->ctx); return; }
     r->log = log.data();
@@ -268,9 +290,15 @@ int main(int argc, char **argv)
         }
     }
     for (size_t r = 0; r < ranks.size(); r++) ranks[r].device = (int)(r % (size_t)D);
+    // every sub-chain on a device of its own: the ranks form an NCCL communicator and the merge runs
+    // distributed over them (BSP_A4_NO_NCCL=1 keeps the gather-on-device-0 path below)
+    unsigned char nccl_id[BSP_COMM_ID_BYTES];
+    const bool use_nccl = ranks.size() > 1 && ranks.size() <= (size_t)D && !getenv("BSP_A4_NO_NCCL") &&
+                          bsp_comm_unique_id(nccl_id, sizeof(nccl_id)) == BSP_OK;
     {
         std::vector<std::thread> th;
-        for (auto &r : ranks) th.emplace_back(run_rank, &r, folder, k, binary);
+        for (size_t r = 0; r < ranks.size(); r++)
+            th.emplace_back(run_rank, &ranks[r], folder, k, binary, use_nccl ? (const void *)nccl_id : nullptr, (int)r, (int)ranks.size());
         for (auto &t : th) t.join();
     }
     int rc = 0;
@@ -280,7 +308,19 @@ int main(int argc, char **argv)
     }
 
     bsp_mat *result = nullptr;
-    if (!rc) {
+    if (!rc && use_nccl) {
+        // bsp_chain_distributed left the product on rank 0; the reference's rank 0 prints the merge log (cu:301)
+        for (size_t n = ranks.size(); n > 1; n = n / 2 + (n & 1))
+            for (size_t i = 0; i + 1 < n; i += 2) printf("multiplying %zu %zu\n", i, i + 1);
+        result = ranks[0].partial;
+        ranks[0].partial = nullptr;
+        bsp_ctx_destroy(probe);
+        probe = ranks[0].ctx; // the result lives in that context
+        if (ranks[0].comm) { bsp_comm_destroy(probe, ranks[0].comm); ranks[0].comm = nullptr; }
+        ranks[0].ctx = nullptr;
+        for (auto *m : ranks[0].mats) bsp_mat_free(probe, m);
+        ranks[0].mats.clear();
+    } else if (!rc) {
         if (ranks.size() == 1) {
             result = ranks[0].partial;
             ranks[0].partial = nullptr;
@@ -331,6 +371,7 @@ int main(int argc, char **argv)
     for (auto &r : ranks) {
         for (auto *m : r.mats) bsp_mat_free(r.ctx, m);
         bsp_mat_free(r.ctx, r.partial);
+        if (r.comm) bsp_comm_destroy(r.ctx, r.comm);
         bsp_ctx_destroy(r.ctx);
     }
     bsp_ctx_destroy(probe);
