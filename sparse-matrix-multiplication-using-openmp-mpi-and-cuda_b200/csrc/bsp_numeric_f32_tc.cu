@@ -115,67 +115,109 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
     const uint32_t tmem = tmem_base_sh;
     constexpr uint32_t idesc = umma_idesc_tf32(M, N);
 
-    uint32_t uses0 = 0, uses1 = 0; // commits issued per stage (all threads track them identically)
-    for (int64_t t = blockIdx.x; t < nnzb_c; t += gridDim.x) {
-        const int64_t p0 = pair_ptr[t], p1 = pair_ptr[t + 1];
-        for (int64_t p = p0; p < p1; p++) {
-            const int s = (int)((p - p0) & 1);
-            const uint32_t uses = s ? uses1 : uses0;
-            if (uses > 0) mbar_wait(bar0 + 8 * s, (uses - 1) & 1); // the MMAs that read this stage are done
-            const int2 pr = pairs[p];
-            const unsigned char *ag = reinterpret_cast<const unsigned char *>(a_vals + (size_t)pr.x * (K * K));
-            const float *bg = b_vals + (size_t)(pr.y & 0x7fffffff) * (K * K);
-            const uint32_t a_s = sbase + s * STAGE, b_s = a_s + A_BYTES;
+    // The CTA's work is one stream of tile products: for every output tile it owns (t = blockIdx.x, += gridDim.x),
+    // the pairs of its list.  Product i+1 is fetched while product i is multiplied and, when i closes its tile,
+    // while the accumulator is read back and stored: A by cp.async (a chunk permutation), B into registers with
+    // plain loads that are transposed into the stage only after the MMAs that last read that stage have retired.
+    constexpr int BBLK = (CHUNKS / 4 + 127) / 128; // 4x4 blocks of B per thread (2 for k = 64, 1 for k = 32 on half the threads)
+    uint32_t uses0 = 0, uses1 = 0;                 // commits issued per stage (all threads track them identically)
+    int64_t t = blockIdx.x;
+    int64_t p = 0, p1 = 0;
+    if (t < nnzb_c) { p = pair_ptr[t]; p1 = pair_ptr[t + 1]; }
+    int2 pr_next = make_int2(0, 0);
+    float4 breg[BBLK][4];
+
+    auto load_a = [&](int s, int ai) {
+        const unsigned char *ag = reinterpret_cast<const unsigned char *>(a_vals + (size_t)ai * (K * K));
+        const uint32_t a_s = sbase + s * STAGE;
 #pragma unroll
-            for (int x = tid; x < CHUNKS; x += 128) {
-                const int row = x / (K / 4), col = x % (K / 4); // chunk `col` of row `row` of the row-major tile
-                cp16(a_s + col * (M * 16) + row * 16, ag + (size_t)x * 16);
-            }
-            // B: 4x4 blocks, transposed in registers (block (kq, nq) = rows 4kq.., columns 4nq..)
+        for (int x = tid; x < CHUNKS; x += 128) {
+            const int row = x / (K / 4), col = x % (K / 4); // chunk `col` of row `row` of the row-major tile
+            cp16(a_s + col * (M * 16) + row * 16, ag + (size_t)x * 16);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    auto load_b = [&](int bi) {
+        const float *bg = b_vals + (size_t)bi * (K * K);
 #pragma unroll
-            for (int x = tid; x < CHUNKS / 4; x += 128) {
+        for (int u = 0; u < BBLK; u++) {
+            const int x = tid + 128 * u;
+            if (x < CHUNKS / 4) {
                 const int kq = x / (K / 4), nq = x % (K / 4);
-                const float4 r0 = *reinterpret_cast<const float4 *>(bg + (size_t)(4 * kq + 0) * K + 4 * nq);
-                const float4 r1 = *reinterpret_cast<const float4 *>(bg + (size_t)(4 * kq + 1) * K + 4 * nq);
-                const float4 r2 = *reinterpret_cast<const float4 *>(bg + (size_t)(4 * kq + 2) * K + 4 * nq);
-                const float4 r3 = *reinterpret_cast<const float4 *>(bg + (size_t)(4 * kq + 3) * K + 4 * nq);
-                float4 *dst = reinterpret_cast<float4 *>(smem + s * STAGE + A_BYTES + kq * (K * 16) + (4 * nq) * 16);
-                dst[0] = make_float4(r0.x, r1.x, r2.x, r3.x);
-                dst[1] = make_float4(r0.y, r1.y, r2.y, r3.y);
-                dst[2] = make_float4(r0.z, r1.z, r2.z, r3.z);
-                dst[3] = make_float4(r0.w, r1.w, r2.w, r3.w);
-            }
-            asm volatile("cp.async.commit_group;" ::: "memory");
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy writes -> visible to the tensor core
-            __syncthreads();
-            if (tid == 0) {
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-                for (int ks = 0; ks < K / 8; ks++) {
-                    const uint64_t da = umma_desc(a_s + ks * 2 * (M * 16), M * 16, 128);
-                    const uint64_t db = umma_desc(b_s + ks * 2 * (K * 16), K * 16, 128);
-                    const uint32_t accumulate = (p > p0 || ks > 0) ? 1u : 0u;
-                    asm volatile(
-                        "{\n\t"
-                        ".reg .pred p;\n\t"
-                        "setp.ne.b32 p, %4, 0;\n\t"
-                        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-                        "}" ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
-                }
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar0 + 8 * s)
-                             : "memory");
+                for (int r = 0; r < 4; r++) breg[u][r] = *reinterpret_cast<const float4 *>(bg + (size_t)(4 * kq + r) * K + 4 * nq);
             }
-            if (s) uses1++; else uses0++;
         }
-        // accumulator complete when the last commit has arrived (tcgen05 ops retire in order)
-        {
-            const int s = (int)((p1 - 1 - p0) & 1);
+    };
+    auto store_b = [&](int s) { // 4x4 blocks transposed in registers: element (n, k) at (k/4)*(K*16) + n*16 + (k%4)*4
+#pragma unroll
+        for (int u = 0; u < BBLK; u++) {
+            const int x = tid + 128 * u;
+            if (x < CHUNKS / 4) {
+                const int kq = x / (K / 4), nq = x % (K / 4);
+                float4 *dst = reinterpret_cast<float4 *>(smem + s * STAGE + A_BYTES + kq * (K * 16) + (4 * nq) * 16);
+                dst[0] = make_float4(breg[u][0].x, breg[u][1].x, breg[u][2].x, breg[u][3].x);
+                dst[1] = make_float4(breg[u][0].y, breg[u][1].y, breg[u][2].y, breg[u][3].y);
+                dst[2] = make_float4(breg[u][0].z, breg[u][1].z, breg[u][2].z, breg[u][3].z);
+                dst[3] = make_float4(breg[u][0].w, breg[u][1].w, breg[u][2].w, breg[u][3].w);
+            }
+        }
+    };
+
+    if (t < nnzb_c) { // first product: nothing to hide behind
+        const int2 pr = pairs[p];
+        load_a(0, pr.x);
+        load_b(pr.y & 0x7fffffff);
+        store_b(0);
+    }
+    int s = 0;
+    bool first_of_tile = true;
+    while (t < nnzb_c) {
+        // the product after this one (same tile, or the first of the CTA's next tile)
+        int64_t tn = t, pn = p + 1, pn1 = p1;
+        if (pn >= p1) {
+            tn = t + gridDim.x;
+            if (tn < nnzb_c) { pn = pair_ptr[tn]; pn1 = pair_ptr[tn + 1]; }
+        }
+        const bool have_next = tn < nnzb_c;
+        const bool last_of_tile = p + 1 >= p1;
+        if (have_next) {
+            const int s1 = s ^ 1;
+            const uint32_t uses = s1 ? uses1 : uses0;
+            if (uses > 0) mbar_wait(bar0 + 8 * s1, (uses - 1) & 1); // the MMAs that read stage s1 are done
+            pr_next = pairs[pn];
+            load_a(s1, pr_next.x);
+            load_b(pr_next.y & 0x7fffffff);
+            asm volatile("cp.async.wait_group 1;" ::: "memory"); // this product's A chunks have landed
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy writes -> visible to the tensor core
+        __syncthreads();
+        if (tid == 0) {
+            const uint32_t a_s = sbase + s * STAGE, b_s = a_s + A_BYTES;
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+            for (int ks = 0; ks < K / 8; ks++) {
+                const uint64_t da = umma_desc(a_s + ks * 2 * (M * 16), M * 16, 128);
+                const uint64_t db = umma_desc(b_s + ks * 2 * (K * 16), K * 16, 128);
+                const uint32_t accumulate = (!first_of_tile || ks > 0) ? 1u : 0u;
+                asm volatile(
+                    "{\n\t"
+                    ".reg .pred p;\n\t"
+                    "setp.ne.b32 p, %4, 0;\n\t"
+                    "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+                    "}" ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar0 + 8 * s)
+                         : "memory");
+        }
+        if (s) uses1++; else uses0++;
+        if (last_of_tile) {
+            // accumulator complete when this product's commit has arrived (tcgen05 ops retire in order)
             mbar_wait(bar0 + 8 * s, ((s ? uses1 : uses0) - 1) & 1);
-        }
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // epilogue: TMEM lanes 32w + i (i < 16) hold tile row 16w + i
-        {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            // epilogue: TMEM lanes 32w + i (i < 16) hold tile row 16w + i
             const int row = 16 * warp + lane;
             const bool valid = lane < 16 && row < K;
             float *out = c_vals + (size_t)t * (K * K) + (size_t)row * K;
@@ -186,13 +228,18 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
                 if (valid) {
 #pragma unroll
                     for (int i = 0; i < 16; i += 4)
-                        *reinterpret_cast<float4 *>(out + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+                        __stcs(reinterpret_cast<float4 *>(out + c0 + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
                 }
             }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            // the next product's __syncthreads orders these TMEM reads before its first MMA
         }
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads(); // TMEM is free for the next tile
+        if (have_next) store_b(s ^ 1); // the B loads have had the MMA issue and the read-back of the accumulator to hide behind
+        first_of_tile = last_of_tile;
+        t = tn; p = pn; p1 = pn1;
+        s ^= 1;
     }
+    __syncthreads();
     if (warp == 0)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
 }

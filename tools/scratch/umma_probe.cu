@@ -9,10 +9,10 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t addr, uint32_t lbo, uint3
     return (uint64_t)((addr >> 4) & 0x3fff) | ((uint64_t)((lbo >> 4) & 0x3fff) << 16) | ((uint64_t)((sbo >> 4) & 0x3fff) << 32) | (1ull << 46);
 }
 template <int K>
-__global__ void probe(const float *A, const float *B, float *out, int swapA, int swapB, int bmajor_mn)
+__global__ void probe(const float *A, const float *B, float *out, int swapA, int swapB, int bmajor_mn, int bsw128)
 {
     constexpr int M = 64, N = K;
-    extern __shared__ __align__(128) unsigned char smem[];
+    extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ __align__(8) uint64_t mbar;
     __shared__ uint32_t tmem_sh;
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -33,7 +33,10 @@ __global__ void probe(const float *A, const float *B, float *out, int swapA, int
     for (int x = tid; x < K * K / 4; x += 128) {
         const int row = x / (K / 4), col = x % (K / 4);
         *(float4 *)(smem + col * (M * 16) + row * 16) = ((const float4 *)A)[x];
-        *(float4 *)(smem + A_BYTES + col * (K * 16) + row * 16) = ((const float4 *)B)[x];
+        if (bsw128) // row-major [k][128 B] with the 128-byte swizzle: chunk n4 of row k at (n4 ^ (k % 8)); atoms of 32 columns LBO apart
+            *(float4 *)(smem + A_BYTES + (col / 8) * (K * 128) + (row / 8) * 1024 + (row % 8) * 128 + (((col % 8) ^ (row % 8)) * 16)) = ((const float4 *)B)[x];
+        else
+            *(float4 *)(smem + A_BYTES + col * (K * 16) + row * 16) = ((const float4 *)B)[x];
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
@@ -41,9 +44,10 @@ __global__ void probe(const float *A, const float *B, float *out, int swapA, int
         asm volatile("tcgen05.fence::after_thread_sync;");
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (0u << 15) | ((uint32_t)bmajor_mn << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
         for (int ks = 0; ks < K / 8; ks++) {
-            const uint32_t a_addr = sbase + ks * 2 * (M * 16), b_addr = sbase + A_BYTES + ks * 128;
+            const uint32_t a_addr = sbase + ks * 2 * (M * 16), b_addr = sbase + A_BYTES + ks * (bsw128 ? 1024 : 128);
             const uint64_t da = swapA ? umma_desc(a_addr, 128, M * 16) : umma_desc(a_addr, M * 16, 128);
-            const uint64_t db = swapB ? umma_desc(b_addr, K * 16, 128) : umma_desc(b_addr, 128, K * 16);
+            uint64_t db = swapB ? umma_desc(b_addr, K * 16, 128) : umma_desc(b_addr, 128, K * 16);
+            if (bsw128) db = umma_desc(b_addr, K * 128, 1024) | (2ull << 61); // SWIZZLE_128B, MN atoms K*128 apart, k-groups 1024 apart
             const uint32_t acc = ks > 0;
             asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
         }
@@ -74,15 +78,15 @@ int main(int argc, char **argv)
         cudaMalloc(&dA, sizeof hA); cudaMalloc(&dB, sizeof hB); cudaMalloc(&dO, sizeof hO);
         cudaMemcpy(dA, hA, sizeof hA, cudaMemcpyHostToDevice); cudaMemcpy(dB, hB, sizeof hB, cudaMemcpyHostToDevice);
         cudaMemset(dO, 0, sizeof hO);
-        const int smem = (K / 4) * 64 * 16 + K * K * 4;
+        const int smem = (K / 4) * 64 * 16 + K * K * 4 + 1024;
         cudaFuncSetAttribute(probe<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        probe<K><<<1, 128, smem>>>(dA, dB, dO, swapA, swapB, bmn);
+        probe<K><<<1, 128, smem>>>(dA, dB, dO, swapA, swapB, bmn, (cfg >> 3) & 1);
         cudaError_t e = cudaDeviceSynchronize();
         cudaMemcpy(hO, dO, sizeof hO, cudaMemcpyDeviceToHost);
         int nz = 0; double err = 0;
         for (int i = 0; i < 128 * K; i++) nz += hO[i] != 0;
         for (int w = 0; w < 2; w++) for (int i = 0; i < 16; i++) for (int n = 0; n < K; n++) err += fabs(hO[(32 * w + i) * K + n] - (100.f * (16 * w + i) + n));
-        printf("cfg swapA=%d swapB=%d bMN=%d : %s nonzeros=%d err(I*R, lanes 32w+i)=%.0f | lane0: %.0f %.0f %.0f %.0f | lane1: %.0f %.0f %.0f | lane16: %.0f %.0f | lane32: %.0f %.0f\n", swapA, swapB, bmn,
+        printf("cfg%d swapA=%d swapB=%d bMN=%d : %s nonzeros=%d err(I*R, lanes 32w+i)=%.0f | lane0: %.0f %.0f %.0f %.0f | lane1: %.0f %.0f %.0f | lane16: %.0f %.0f | lane32: %.0f %.0f\n", cfg, swapA, swapB, bmn,
                cudaGetErrorString(e), nz, err, hO[0], hO[1], hO[2], hO[3], hO[K], hO[K + 1], hO[K + 2], hO[16 * K], hO[16 * K + 1], hO[32 * K], hO[32 * K + 1]);
         cudaFree(dA); cudaFree(dB); cudaFree(dO);
     }
