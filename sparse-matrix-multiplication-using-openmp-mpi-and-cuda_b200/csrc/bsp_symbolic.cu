@@ -408,6 +408,159 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     for (int x = tid; x < P; x += FILL_THREADS) pairs[pbase + x] = sp[x];
 }
 
+// ---- fill, long rows: one CTA per row, every warp owns a range of output tiles -----------------------
+// Rows beyond the shared-memory classes (15 000 .. 2^18 tile products: two thirds of the products of an
+// R-MAT pattern).  sym_fill_global_kernel below keeps their per-tile counters in global memory and, when
+// some tile has more than a few pairs (almost every such row has one), places the pairs entry by entry
+// with a CTA barrier after each: ncu showed 10 % of the issue slots used and the barrier as the top stall.
+// Here the counters live in shared memory (4 bytes per OUTPUT TILE, not per product: a row with 250 000
+// products has 16 000 tiles) and the placement needs no CTA barrier: after counting, the row's tiles are cut
+// into 16 ranges of equal pair counts; the B rows are sorted by block column, so a tile range is a column
+// range and a contiguous piece of every B row (two binary searches per entry, 32 entries at a time, one per
+// lane).  Every warp walks the A row alone, in ascending inner index, over its own piece of each B row: it
+// is the only writer of its tiles' cursors, the pieces of one B row fall into different tiles, and a
+// __syncwarp() between two entries keeps the append order -- the order the arithmetic needs, by construction.
+constexpr int BIG_THREADS = 512;
+constexpr int BIG_WARPS = BIG_THREADS / 32;
+
+__host__ __device__ inline size_t big_smem_bytes(int words, int tcap) { return 8 * (size_t)words + 4 * ((size_t)tcap + 4); }
+
+__global__ void __launch_bounds__(BIG_THREADS, 2)
+sym_fill_big_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
+                    const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
+                    const int32_t *__restrict__ b_colidx, int nbc, int words, const int32_t *__restrict__ c_rowptr,
+                    const int64_t *__restrict__ row_prod_ptr, int32_t *c_colidx, int64_t *__restrict__ pair_ptr,
+                    int2 *pairs)
+{
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ int sm33[33];
+    __shared__ int wt0[BIG_WARPS + 1], wc0[BIG_WARPS + 1]; // first tile / first block column of every warp's range
+    uint32_t *bm = smem;
+    uint32_t *wrank = bm + words;
+    int *cur = (int *)(wrank + words); // [T + 1] pairs per tile, then first slot, then cursor (row-local)
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int row = rowlist[blockIdx.x];
+    const int cbase = c_rowptr[row], T = c_rowptr[row + 1] - cbase;
+    const int64_t pbase = row_prod_ptr[row];
+    const int P = (int)(row_prod_ptr[row + 1] - pbase);
+    const int a0 = a_rowptr[row], a1 = a_rowptr[row + 1];
+    for (int w = tid; w < words; w += BIG_THREADS) bm[w] = 0u;
+    for (int t = tid; t < T + 1; t += BIG_THREADS) cur[t] = 0;
+    __syncthreads();
+    // A. column bitmap of the row (warps over A entries, lanes over B row j)
+    for (int p = a0 + warp; p < a1; p += BIG_WARPS) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        for_each_tile_of_row(b_colidx, b_rowptr[j], b_rowptr[j + 1], lane,
+                             [&](int, int c) { atomicOr(&bm[c >> 5], 1u << (c & 31)); });
+    }
+    __syncthreads();
+    // B. rank table + sorted colidx of the C row
+    int carry = 0;
+    for (int w0 = 0; w0 < words; w0 += BIG_THREADS) {
+        const int w = w0 + tid;
+        const uint32_t bits = w < words ? bm[w] : 0u;
+        int tot;
+        const int ex = block_excl_scan_i32(__popc(bits), sm33, &tot);
+        if (w < words) {
+            wrank[w] = (uint32_t)(carry + ex);
+            uint32_t b = bits;
+            int o = cbase + carry + ex;
+            while (b) {
+                const int bit = __ffs(b) - 1;
+                b &= b - 1;
+                c_colidx[o++] = w * 32 + bit;
+            }
+        }
+        carry += tot;
+    }
+    __syncthreads();
+    // C. pairs per tile
+    for (int p = a0 + warp; p < a1; p += BIG_WARPS) {
+        const int j = a_colidx[p];
+        if (j >= b_nbr) continue;
+        for_each_tile_of_row(b_colidx, b_rowptr[j], b_rowptr[j + 1], lane, [&](int, int c) {
+            const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+            atomicAdd(&cur[t], 1);
+        });
+    }
+    __syncthreads();
+    // D. counts -> first slot of every tile (every thread scans a contiguous piece serially, one block scan joins
+    //    the pieces); pair_ptr of the row
+    {
+        const int ch = (T + BIG_THREADS - 1) / BIG_THREADS;
+        const int t0 = min(tid * ch, T), t1 = min(t0 + ch, T);
+        int sum = 0;
+        for (int t = t0; t < t1; t++) sum += cur[t];
+        int tot;
+        int ex = block_excl_scan_i32(sum, sm33, &tot);
+        for (int t = t0; t < t1; t++) { const int v = cur[t]; cur[t] = ex; ex += v; }
+        if (tid == 0) cur[T] = P;
+        __syncthreads();
+        for (int t = tid; t < T; t += BIG_THREADS) pair_ptr[(size_t)cbase + t] = pbase + cur[t];
+    }
+    // E. the warps' tile ranges: equal shares of the row's pairs; the range of warp w starts at the first tile whose
+    //    first slot is at or beyond w * P / 16
+    if (tid <= BIG_WARPS) {
+        int t = T;
+        if (tid < BIG_WARPS) {
+            const int want = (int)((long long)P * tid / BIG_WARPS);
+            int lo = 0, hi = T;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (cur[mid] >= want) hi = mid; else lo = mid + 1;
+            }
+            t = tid == 0 ? 0 : lo;
+        }
+        wt0[tid] = t;
+    }
+    __threadfence_block(); // c_colidx of this row was written by this CTA in step B
+    __syncthreads();
+    if (tid <= BIG_WARPS) wc0[tid] = wt0[tid] < T ? c_colidx[cbase + wt0[tid]] : nbc;
+    __syncthreads();
+    // F. ordered placement, warp by warp
+    {
+        const int c_lo = wc0[warp], c_hi = wc0[warp + 1];
+        if (c_lo < c_hi) {
+            for (int e0 = a0; e0 < a1; e0 += 32) {
+                // this lane's entry: the piece [lo, hi) of its B row that falls into the warp's column range
+                int lo = 0, hi = 0;
+                if (e0 + lane < a1) {
+                    const int j = a_colidx[e0 + lane];
+                    if (j < b_nbr) {
+                        const int b0 = b_rowptr[j], b1 = b_rowptr[j + 1];
+                        int l = b0, h = b1;
+                        while (l < h) { const int m = (l + h) >> 1; if (b_colidx[m] < c_lo) l = m + 1; else h = m; }
+                        lo = l;
+                        h = b1;
+                        if (c_hi < nbc) { while (l < h) { const int m = (l + h) >> 1; if (b_colidx[m] < c_hi) l = m + 1; else h = m; } hi = l; }
+                        else hi = b1;
+                    }
+                }
+                unsigned todo = __ballot_sync(0xffffffffu, lo < hi); // entries with a non-empty piece, ascending
+                while (todo) {
+                    const int ee = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const int plo = __shfl_sync(0xffffffffu, lo, ee), phi = __shfl_sync(0xffffffffu, hi, ee);
+                    const int p = e0 + ee;
+                    for (int q = plo + lane; q < phi; q += 32) {
+                        const int c = b_colidx[q];
+                        const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+                        const int pos = cur[t];
+                        cur[t] = pos + 1;
+                        pairs[pbase + pos] = make_int2(p, q);
+                    }
+                    __syncwarp(); // the next entry may append to the same tiles
+                }
+            }
+        }
+    }
+    __threadfence_block();
+    __syncthreads();
+    // G. the cursors are the tile ends now: flag the last pair of every tile (sign bit of .y)
+    for (int t = tid; t < T; t += BIG_THREADS) pairs[pbase + cur[t] - 1].y |= (int)0x80000000;
+}
+
 // ---- fill, global-memory variant: rows whose pair list does not fit in shared memory ----------
 // Same algorithm with the per-tile counters/cursors kept in the row's own pair_ptr slots: slot t
 // holds the count, then the first free slot of tile t; after the placement it holds the END of
@@ -984,14 +1137,14 @@ sym_fill_tiny_kernel(const int32_t *__restrict__ rowlist, int nrows, const int32
 // ---- rows -> capacity classes -----------------------------------------------------------------
 // class c rows go to lists[c * nbr ...]; counts[c] = rows in class c.  A row with P tile
 // products fits class c when P <= caps[c]; larger than every cap -> class NCLASS-1 (global).
-constexpr int NCLASS = 8; // 6, 7: rows with many pairs per tile whose bit matrix fits DENSE_M0 / DENSE_M1 words;
+constexpr int NCLASS = 9; // 8: long rows, one CTA per row with per-warp tile ranges (counters in shared memory); 6, 7: rows with many pairs per tile whose bit matrix fits DENSE_M0 / DENSE_M1 words;
                           // 0: tiny rows (warp + sort), 1..3: shared-memory CTA classes, 4: global-memory CTA,
                           // 5: rows so long that one CTA would be the tail of the pass -> multi-launch path
 
 __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowptr,
                                      const int32_t *__restrict__ row_cnt, const int32_t *__restrict__ row_prod,
                                      int cap0, int cap1, int cap2, int tcap0, int tcap1, int tcap2, int acap,
-                                     int tiny_ok, int hv_min, int dense_ok, int32_t *__restrict__ lists,
+                                     int tiny_ok, int hv_min, int dense_ok, int big_tcap, int32_t *__restrict__ lists,
                                      int32_t *__restrict__ counts)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1001,12 +1154,15 @@ __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowp
     int cls = (P <= cap0 && T <= tcap0) ? 1 : ((P <= cap1 && T <= tcap1) ? 2 : ((P <= cap2 && T <= tcap2) ? 3 : 4));
     if (nA > acap) cls = 4;                                  // A row too long for the shared-memory entry table
     if (tiny_ok && P <= TINY_P && nA <= TINY_A) cls = 0;     // warp-per-row sort
-    if (cls == 4 && P > hv_min) cls = 5;                     // spread over the whole GPU
+    // spread over the whole GPU -- unless the row's counters fit the one-CTA kernel with per-warp tile ranges, which
+    // is the cheaper of the two up to a few million products (R-MAT hub row, 3.3e5 products: 0.5 ms there, 1.0 ms here)
+    if (cls == 4 && P > hv_min && (T > big_tcap || P > 8 * (long long)hv_min)) cls = 5;
     if (dense_ok && cls != 0 && P >= dense_ok * T) {   // dense_ok = minimum tile products per output tile  // many pairs per tile: bit-matrix placement
         const int mw = T <= DENSE_M1 ? dense_need_words(T, nA) : DENSE_M1 + 1;
         if (mw <= DENSE_M0) cls = 6;
         else if (mw <= DENSE_M1) cls = 7;
     }
+    if (cls == 4 && T <= big_tcap) cls = 8;                  // counters fit in shared memory: per-warp tile ranges
     const int slot = atomicAdd(&counts[cls], 1);
     lists[(size_t)cls * nbr + slot] = row;
 }
@@ -1133,6 +1289,11 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         if (const char *e = getenv("BSP_SYM_DENSE_RATIO")) { const int v = atoi(e); if (v > 0) dense_ok = v; }
     // the tiny-row kernel packs the block column into 27 bits; BSP_SYM_CAPS (a test hook) also switches it off
     const int tiny_ok = (B->nbc < (1 << 27) && !getenv("BSP_SYM_CAPS")) ? 1 : 0;
+    // long rows with at most big_tcap output tiles keep their per-tile counters in shared memory (two CTAs per SM);
+    // BSP_SYM_BIG=0 sends them to the global-memory kernel instead (comparison / test hook)
+    int big_tcap = 0;
+    if (8 * (size_t)words + 64 < 110 * 1024) big_tcap = (int)((110 * 1024 - 8 * (size_t)words) / 4) - 8;
+    if (const char *e = getenv("BSP_SYM_BIG")) { if (atoi(e) == 0) big_tcap = 0; }
     for (int c = 0; c < 3; c++) {
         if (caps[c] > 60000) caps[c] = 60000; // tile ranks are kept as 16-bit values in shared memory
         if (tcaps[c] > caps[c]) tcaps[c] = caps[c];
@@ -1159,7 +1320,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         }
         classify_rows_kernel<<<(nbr + 255) / 256, 256, 0, ctx->stream>>>(nbr, A->rowptr, row_cnt, row_prod, caps[0],
                                                                         caps[1], caps[2], tcaps[0], tcaps[1], tcaps[2],
-                                                                        acap, tiny_ok, hv_min, dense_ok, lists, counts);
+                                                                        acap, tiny_ok, hv_min, dense_ok, big_tcap, lists, counts);
         BSP_LAUNCH_CHECK(ctx);
     }
     bsp_trace_mark(ctx, "sym_count");
@@ -1259,6 +1420,14 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         sym_fill_dense_kernel<<<ncls[c], DENSE_THREADS, bytes, ctx->stream>>>(
             lists + (size_t)c * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, mcap, out->c_rowptr,
             row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
+        BSP_LAUNCH_CHECK(ctx);
+    }
+    if (ncls[8] > 0) {
+        const size_t bytes = big_smem_bytes(words, big_tcap);
+        BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        sym_fill_big_kernel<<<ncls[8], BIG_THREADS, bytes, ctx->stream>>>(lists + (size_t)8 * nbr, A->rowptr, A->colidx, B->nbr,
+                                                                         B->rowptr, B->colidx, B->nbc, words, out->c_rowptr,
+                                                                         row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
     }
     if (ncls[5] > 0) BSP_TRY(fill_heavy_rows(ctx, A, B, lists + (size_t)5 * nbr, ncls[5], words, out, row_prod_ptr));

@@ -306,6 +306,10 @@ def test_symbolic_row_classes_and_generic_numeric(ctx):
         for caps in ("16,64,256", "4,8,16", "100000,100000,100000"):
             os.environ["BSP_SYM_CAPS"] = caps
             assert_same(ctx.helper(dev(ctx, a), dev(ctx, b)), ref)
+            # rows beyond the classes: the per-warp-range kernel (default) and the global-memory kernel
+            os.environ["BSP_SYM_BIG"] = "0"
+            assert_same(ctx.helper(dev(ctx, a), dev(ctx, b)), ref)
+            os.environ.pop("BSP_SYM_BIG", None)
         os.environ["BSP_FORCE_GENERIC"] = "1"
         with bspgemm.Context(0) as c2:
             st = bspgemm.Stats()
@@ -313,6 +317,7 @@ def test_symbolic_row_classes_and_generic_numeric(ctx):
             assert st.numeric_path == 0
     finally:
         os.environ.pop("BSP_SYM_CAPS", None)
+        os.environ.pop("BSP_SYM_BIG", None)
         os.environ.pop("BSP_FORCE_GENERIC", None)
 
 
