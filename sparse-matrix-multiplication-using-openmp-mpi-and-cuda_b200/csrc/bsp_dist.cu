@@ -142,7 +142,7 @@ __global__ void clamp_rowptr_kernel(int32_t *__restrict__ rp, int n, int32_t s0)
     if (i < n) rp[i] = (rp[i] > s0 ? rp[i] : s0) - s0;
 }
 
-// estimated cost of every block row of A*B in tile products (warp per row): the balance measure of bsp_panel_bounds
+// tile products of every block row of A*B (warp per row): the balance measure of bsp_panel_bounds
 __global__ void row_work_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t *__restrict__ a_colidx,
                                 int b_nbr, const int32_t *__restrict__ b_rowptr, int32_t *__restrict__ work)
 {
@@ -158,10 +158,6 @@ __global__ void row_work_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr,
     }
 #pragma unroll
     for (int d = 16; d; d >>= 1) w += __shfl_xor_sync(0xffffffffu, w, d);
-    // cost, not just products: a row of 15 000 .. 2^18 products goes through the one-CTA-per-row symbolic kernel
-    // on global memory (17 products/ns against 45 for the shared-memory classes; the numeric pass runs at 5.3
-    // for both), i.e. about 1/6 more time per product.  Keep in step with the capacity classes of bsp_symbolic.cu.
-    if (w > 15000) w += w / 6;
     if (lane == 0) work[row] = row < a_nbr ? (int32_t)(w > 0x7fffffffLL ? 0x7fffffffLL : w) : 0;
 }
 

@@ -420,18 +420,21 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
 // lane).  Every warp walks the A row alone, in ascending inner index, over its own piece of each B row: it
 // is the only writer of its tiles' cursors, the pieces of one B row fall into different tiles, and a
 // __syncwarp() between two entries keeps the append order -- the order the arithmetic needs, by construction.
-constexpr int BIG_THREADS = 512;
-constexpr int BIG_WARPS = BIG_THREADS / 32;
+constexpr int BIG_WARPS_LONG = 16; // long rows: 512 threads
+// (a 4-warp instance of the same kernel for rows of a few thousand products -- configs[1]: 6.7 k per row -- was measured:
+// 1.40 ms against 0.94 ms for the CTA-per-row shared-memory kernel; the pieces of a B row per warp are too short there)
 
 __host__ __device__ inline size_t big_smem_bytes(int words, int tcap) { return 8 * (size_t)words + 4 * ((size_t)tcap + 4); }
 
-__global__ void __launch_bounds__(BIG_THREADS, 2)
+template <int BIG_WARPS>
+__global__ void __launch_bounds__(BIG_WARPS * 32, BIG_WARPS >= 16 ? 2 : 8)
 sym_fill_big_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
                     const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
                     const int32_t *__restrict__ b_colidx, int nbc, int words, const int32_t *__restrict__ c_rowptr,
                     const int64_t *__restrict__ row_prod_ptr, int32_t *c_colidx, int64_t *__restrict__ pair_ptr,
                     int2 *pairs)
 {
+    constexpr int BIG_THREADS = BIG_WARPS * 32;
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ int sm33[33];
     __shared__ int wt0[BIG_WARPS + 1], wc0[BIG_WARPS + 1]; // first tile / first block column of every warp's range
@@ -1424,8 +1427,8 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     }
     if (ncls[8] > 0) {
         const size_t bytes = big_smem_bytes(words, big_tcap);
-        BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        sym_fill_big_kernel<<<ncls[8], BIG_THREADS, bytes, ctx->stream>>>(lists + (size_t)8 * nbr, A->rowptr, A->colidx, B->nbr,
+        BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_big_kernel<BIG_WARPS_LONG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        sym_fill_big_kernel<BIG_WARPS_LONG><<<ncls[8], BIG_WARPS_LONG * 32, bytes, ctx->stream>>>(lists + (size_t)8 * nbr, A->rowptr, A->colidx, B->nbr,
                                                                          B->rowptr, B->colidx, B->nbc, words, out->c_rowptr,
                                                                          row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
