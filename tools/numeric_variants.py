@@ -12,7 +12,7 @@ sys.path.insert(0, os.path.join(ROOT, "sparse-matrix-multiplication-using-openmp
 import bsp_gen  # noqa: E402
 import bspgemm  # noqa: E402
 
-KEYS = ("BSP_NUM_KERNEL", "BSP_NUM_PANEL_MB", "BSP_NUM_Q", "BSP_NUM_WARPS", "BSP_NUM_MINB", "BSP_NUM_MACV", "BSP_NUM_SORT", "BSP_HV_MIN_P", "BSP_SYM_NO_DENSE", "BSP_SYM_DENSE_RATIO", "BSP_SYM_BIG", "BSP_SYM_MED")
+KEYS = ("BSP_NUM_KERNEL", "BSP_NUM_PANEL_MB", "BSP_NUM_Q", "BSP_NUM_WARPS", "BSP_NUM_MINB", "BSP_NUM_MACV", "BSP_NUM_SORT", "BSP_HV_MIN_P", "BSP_SYM_NO_DENSE", "BSP_SYM_DENSE_RATIO", "BSP_SYM_BIG")
 
 
 def main():
