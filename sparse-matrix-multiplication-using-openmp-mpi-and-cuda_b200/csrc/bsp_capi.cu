@@ -234,6 +234,7 @@ int bsp_ctx_create(int device, void *stream, bsp_ctx **out)
     ctx->pinned_bytes = 4096;
     BSP_CUDA(ctx, cudaMallocHost(&ctx->pinned, ctx->pinned_bytes));
     memset(ctx->pinned, 0, ctx->pinned_bytes);
+    BSP_CUDA(ctx, cudaHostGetDevicePointer(&ctx->pinned_dev, ctx->pinned, 0));
     BSP_CUDA(ctx, cudaMalloc(&ctx->d_counters, 256));
     BSP_CUDA(ctx, cudaMemset(ctx->d_counters, 0, 256));
     {
@@ -642,12 +643,16 @@ int bsp_multiply_host(bsp_ctx *ctx, int32_t k, int32_t rows_a, int32_t cols_a, i
 {
     if (!ctx || !nnzb_c) return BSP_ERR_ARG;
     bsp_mat *A = nullptr, *B = nullptr, *C = nullptr;
+    auto now_ms = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const char *th = getenv("BSP_TRACE_HOST"); // host-side timeline of this call on stderr (adds no device waits)
+    const bool trace_host = ctx->trace || (th && th[0] == '1');
+    const double t_start = now_ms();
     int rc = bsp_mat_from_coo(ctx, rows_a, cols_a, k, nnzb_a, brow_a, bcol_a, vals_a, &A);
+    const double t_a = now_ms();
     if (rc == BSP_OK) rc = bsp_mat_from_coo(ctx, rows_b, cols_b, k, nnzb_b, brow_b, bcol_b, vals_b, &B);
+    const double t_b = now_ms();
     const bool want_out = brow_c || bcol_c || vals_c;
     const char *nopipe = getenv("BSP_NO_PIPELINE");
-    auto now_ms = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-    const double t_start = now_ms();
     if (rc == BSP_OK && (!want_out || A->nnzb < 65536 || !ctx->copy_stream || (nopipe && nopipe[0] == '1'))) {
         // small problem or size query: one product, one download
         rc = bsp_spgemm(ctx, A, B, &C, stats);
@@ -732,9 +737,10 @@ int bsp_multiply_host(bsp_ctx *ctx, int32_t k, int32_t rows_a, int32_t cols_a, i
     const double t_copied = now_ms();
     for (int p = 0; p < NP; p++) { bsp_release(ctx, d_brow[p]); bsp_mat_free(ctx, panels[p]); }
     bsp_mat_free(ctx, A); bsp_mat_free(ctx, B);
-    if (ctx->trace)
-        fprintf(stderr, "[bsp trace] multiply_host: panels issued after %.1f ms, downloads done after %.1f ms\n",
-                t_panels - t_start, t_copied - t_start);
+    if (trace_host)
+        fprintf(stderr, "[bsp trace] multiply_host: A on the device after %.1f ms, B after %.1f, panels issued after %.1f, "
+                        "downloads done after %.1f, buffers released after %.1f\n",
+                t_a - t_start, t_b - t_start, t_panels - t_start, t_copied - t_start, now_ms() - t_start);
     if (rc == BSP_OK) {
         *nnzb_c = done;
         tot.nnzb_a = nnzb_a;

@@ -25,6 +25,7 @@ struct bsp_ctx {
     int64_t launches;
     cudaEvent_t ev[4];
     void *pinned;        // small pinned staging area for scalar read-backs
+    void *pinned_dev;    // the same area as the device sees it (mapped): bsp_publish stores into it from a kernel
     size_t pinned_bytes;
     char *io_buf[2];     // pinned staging pieces of the binary reader/writer, allocated on first use
     cudaEvent_t io_ev[2];
@@ -92,6 +93,18 @@ static inline void bsp_release(bsp_ctx *ctx, void *p)
 {
     if (p) cudaFreeAsync(p, ctx->stream);
 }
+
+// Scalar read-backs (tile totals, class counts, refold counter): up to four runs of 32-bit words are stored into
+// ctx->pinned at the given byte offsets by a one-warp kernel on ctx->stream; the caller reads them after it has
+// waited on the stream.  Not a device->host copy on purpose: those queue in the copy engine behind a bulk
+// download running on ctx->copy_stream (bsp_multiply_host), and the next panel's symbolic pass would wait for it.
+struct bsp_publish_list {
+    const void *src[4];
+    uint32_t offset[4]; // bytes into ctx->pinned, multiple of 4
+    uint32_t words[4];
+    int n;
+};
+int bsp_publish(bsp_ctx *ctx, const bsp_publish_list &list);
 
 // BSP_TRACE=1: mark a point on the stream; bsp_trace_dump prints the gaps between marks
 static inline void bsp_trace_mark(bsp_ctx *ctx, const char *label)

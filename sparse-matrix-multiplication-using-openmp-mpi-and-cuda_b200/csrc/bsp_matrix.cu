@@ -206,7 +206,12 @@ int bsp_ingest_coo(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, int32_t 
     BSP_LAUNCH_CHECK(ctx);
     BSP_TRY(bsp_scan_i32(ctx, keep, pos, nnzb + 1, nullptr));
     int32_t *h_uniq = (int32_t *)ctx->pinned;
-    BSP_CUDA(ctx, cudaMemcpyAsync(h_uniq, pos + nnzb, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    {
+        bsp_publish_list pl = {};
+        pl.n = 1;
+        pl.src[0] = pos + nnzb; pl.offset[0] = 0; pl.words[0] = 1;
+        BSP_TRY(bsp_publish(ctx, pl));
+    }
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     m->nnzb = *h_uniq;
     BSP_TRY(bsp_alloc(ctx, &m->colidx, (size_t)m->nnzb));
@@ -250,7 +255,12 @@ int bsp_prune_device(bsp_ctx *ctx, bsp_mat *m)
     }
     BSP_TRY(bsp_scan_i32(ctx, keep, pos, m->nnzb + 1, nullptr));
     int32_t *h_kept = (int32_t *)ctx->pinned;
-    BSP_CUDA(ctx, cudaMemcpyAsync(h_kept, pos + m->nnzb, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    {
+        bsp_publish_list pl = {};
+        pl.n = 1;
+        pl.src[0] = pos + m->nnzb; pl.offset[0] = 0; pl.words[0] = 1;
+        BSP_TRY(bsp_publish(ctx, pl));
+    }
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const int64_t kept = *h_kept;
     if (kept != m->nnzb) {

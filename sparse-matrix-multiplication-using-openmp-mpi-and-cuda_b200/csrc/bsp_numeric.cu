@@ -812,9 +812,11 @@ int bsp_numeric(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_symb
         else BSP_TRY(launch_bigtile<32>(ctx, A, B, sym, A->nbr, sym->c_rowptr, c_vals));
         if (path) *path = k;
         if (exact_refolds) {
-            unsigned long long *h = (unsigned long long *)((char *)ctx->pinned + 64);
-            // the caller reads *h after its event sync (bsp_capi.cu)
-            BSP_CUDA(ctx, cudaMemcpyAsync(h, ctx->d_counters, sizeof(*h), cudaMemcpyDeviceToHost, ctx->stream));
+            // the caller reads the counter at ctx->pinned + 64 after its event sync (bsp_capi.cu)
+            bsp_publish_list pl = {};
+            pl.n = 1;
+            pl.src[0] = ctx->d_counters; pl.offset[0] = 64; pl.words[0] = 2;
+            BSP_TRY(bsp_publish(ctx, pl));
         }
         return BSP_OK;
     }

@@ -130,3 +130,26 @@ int bsp_scan_i32_to_i64(bsp_ctx *ctx, const int32_t *in, int64_t *out, int64_t n
 {
     return scan_impl<int64_t>(ctx, in, out, n, nullptr);
 }
+
+// ---- scalar read-backs without the copy engine (bsp_internal.h) -------------------------------------
+namespace {
+__global__ void publish_kernel(const __grid_constant__ bsp_publish_list list, uint32_t *__restrict__ host_words)
+{
+    for (int s = 0; s < list.n; s++) {
+        const uint32_t *src = (const uint32_t *)list.src[s];
+        uint32_t *dst = host_words + list.offset[s] / 4;
+        for (uint32_t i = threadIdx.x; i < list.words[s]; i += blockDim.x) dst[i] = src[i];
+    }
+    __threadfence_system();
+}
+} // namespace
+
+int bsp_publish(bsp_ctx *ctx, const bsp_publish_list &list)
+{
+    for (int s = 0; s < list.n; s++)
+        if ((list.offset[s] & 3) || (size_t)list.offset[s] + 4 * (size_t)list.words[s] > ctx->pinned_bytes)
+            BSP_FAIL(ctx, BSP_ERR_ARG, "bsp_publish: run %d does not fit the pinned area", s);
+    publish_kernel<<<1, 32, 0, ctx->stream>>>(list, (uint32_t *)ctx->pinned_dev);
+    BSP_LAUNCH_CHECK(ctx);
+    return BSP_OK;
+}

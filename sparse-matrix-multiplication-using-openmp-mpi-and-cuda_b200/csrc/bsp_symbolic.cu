@@ -1330,13 +1330,19 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     BSP_TRY(bsp_scan_i32(ctx, row_cnt, out->c_rowptr, (int64_t)nbr + 1, nullptr));
     BSP_TRY(bsp_scan_i32_to_i64(ctx, row_prod, row_prod_ptr, (int64_t)nbr + 1));
 
-    // totals -> host (the one unavoidable sync of the pass: C and the pair lists are sized from them)
+    // totals -> host (the one unavoidable sync of the pass: C and the pair lists are sized from them); a kernel
+    // store into mapped pinned memory, not a copy -- see bsp_publish
     int32_t *h_nnzb = (int32_t *)ctx->pinned;
     int64_t *h_nprod = (int64_t *)((char *)ctx->pinned + 8);
     int32_t *h_counts = (int32_t *)((char *)ctx->pinned + 16);
-    BSP_CUDA(ctx, cudaMemcpyAsync(h_nnzb, out->c_rowptr + nbr, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    BSP_CUDA(ctx, cudaMemcpyAsync(h_nprod, row_prod_ptr + nbr, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    BSP_CUDA(ctx, cudaMemcpyAsync(h_counts, counts, (NCLASS + 2) * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    {
+        bsp_publish_list pl = {};
+        pl.n = 3;
+        pl.src[0] = out->c_rowptr + nbr; pl.offset[0] = 0;  pl.words[0] = 1;
+        pl.src[1] = row_prod_ptr + nbr;  pl.offset[1] = 8;  pl.words[1] = 2;
+        pl.src[2] = counts;              pl.offset[2] = 16; pl.words[2] = NCLASS + 2;
+        BSP_TRY(bsp_publish(ctx, pl));
+    }
     bsp_trace_mark(ctx, "sym_scans");
     BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     out->nnzb_c = *h_nnzb;
@@ -1352,7 +1358,12 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
         int64_t *cnt64 = nullptr;
         BSP_TRY(sc.alloc(&cnt64, (size_t)nbr + 1));
         BSP_TRY(bsp_scan_i32_to_i64(ctx, row_cnt, cnt64, (int64_t)nbr + 1));
-        BSP_CUDA(ctx, cudaMemcpyAsync(h_nprod, cnt64 + nbr, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+        {
+            bsp_publish_list pl = {};
+            pl.n = 1;
+            pl.src[0] = cnt64 + nbr; pl.offset[0] = 8; pl.words[0] = 2;
+            BSP_TRY(bsp_publish(ctx, pl));
+        }
         BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         if (*h_nprod > 0x7fffffffLL) BSP_FAIL(ctx, BSP_ERR_LIMIT, "product has more than 2^31-1 tiles");
     }
