@@ -6,9 +6,9 @@
 // accumulator and read back once with tcgen05.ld -- the tile never leaves the tensor memory
 // between pairs.
 //
-// One CTA (4 warps) per output tile at a time, two shared-memory stages:
-//   all threads : stage the tiles of pair p into stage p&1 in the canonical no-swizzle K-major
-//                 UMMA layout (8-row x 16-byte core matrices):
+// One CTA (4 warps) walks a stream of tile products, two shared-memory stages and two TMEM accumulators:
+//   all threads : stage the tiles of product i+1 into stage (i+1)&1 in the canonical no-swizzle K-major
+//                 UMMA layout (8-row x 16-byte core matrices) while product i is multiplied:
 //                   A: element (m, k)  at (k/4)*(64*16) + m*16 + (k%4)*4     LBO = 1024, SBO = 128
 //                      a 16-byte chunk of the row-major tile is already one core-matrix row, so
 //                      A is a pure chunk permutation done by cp.async;
@@ -20,9 +20,14 @@
 //                 produced zeros in a probe on this toolchain -- tools/scratch/umma_probe.cu.)
 //   one thread  : K/8 tcgen05.mma (M=64, N=K, K=8 each), then tcgen05.commit -> the stage's mbarrier
 //   epilogue    : warp w reads TMEM lanes 32w..32w+15 = tile rows 16w..16w+15 (the M=64
-//                 accumulator layout uses 16 lanes of every sub-partition) and stores them.
+//                 accumulator layout uses 16 lanes of every sub-partition) and stores them -- one
+//                 product later, while the next tile is multiplied into the other accumulator.
+// The pair of product i+2 and the pair_ptr bounds of the next chunk of tiles are fetched ahead, so the
+// loop waits for no index load (the first version spent ~1.5 of its ~5 us per product there).
 // For k = 32 the M=64 instruction runs with its upper 32 rows unused (the tile product is far
 // below the tensor pipe's rate either way: 8 flop per byte moved).
+#include <vector>
+
 #include "bsp_internal.h"
 
 namespace {
@@ -66,30 +71,46 @@ __host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N)
            ((uint32_t)(M >> 4) << 24);
 }
 
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float *v)
+// 16 TMEM lanes x (8 * n) columns per warp, load and wait in one statement (no use of the registers can be scheduled
+// between them).  Lane i gets, for every group j of 8 columns: v[4j], v[4j+1] = row i/4, columns 8j + 2(i%4) + {0, 1};
+// v[4j+2], v[4j+3] = row i/4 + 8, same columns -- four lanes hold 32 contiguous bytes of a row.
+__device__ __forceinline__ void tmem_ld_16x256b_x4(uint32_t taddr, uint32_t *v)
 {
-    uint32_t r[16];
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
+        "tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_16x256b_x8(uint32_t taddr, uint32_t *v)
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
 }
 
-template <int K>
+// One entry of the CTA's product stream.  tb: -2 = the stream has ended, -1 = next product of the current chunk,
+// >= 0 = first product of a new chunk whose first output tile is tb.
+struct tc_entry {
+    int2 pr;
+    int64_t tb;
+};
+
+template <int K, bool PROF>
 __global__ void __launch_bounds__(128)
 f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals, const int64_t *__restrict__ pair_ptr,
-              const int2 *__restrict__ pairs, int64_t nnzb_c, float *__restrict__ c_vals)
+              const int2 *__restrict__ pairs, int64_t nnzb_c, int tch, float *__restrict__ c_vals, long long *__restrict__ prof)
 {
     constexpr int M = 64, N = K;
     constexpr int A_BYTES = (K / 4) * M * 16;  // chunk-major A: [kc][m] 16-byte chunks (64 rows, K=32 uses 32)
     constexpr int B_BYTES = (K / 4) * N * 16;  // chunk-major B^T: [kc][n] 16-byte chunks
     constexpr int STAGE = A_BYTES + B_BYTES;
     constexpr int CHUNKS = K * K / 4;          // 16-byte chunks per tile
-    constexpr int TMEM_COLS = N < 32 ? 32 : N;
+    constexpr int TMEM_COLS = 2 * N;           // two accumulators: one is read back while the next tile is multiplied
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) uint64_t mbar[2];
     __shared__ uint32_t tmem_base_sh;
@@ -115,25 +136,53 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
     const uint32_t tmem = tmem_base_sh;
     constexpr uint32_t idesc = umma_idesc_tf32(M, N);
 
-    // The CTA's work is one stream of tile products: for every output tile it owns (t = blockIdx.x, += gridDim.x),
-    // the pairs of its list.  Product i+1 is fetched while product i is multiplied and, when i closes its tile,
-    // while the accumulator is read back and stored: A by cp.async (a chunk permutation), B into registers with
-    // plain loads that are transposed into the stage only after the MMAs that last read that stage have retired.
+    // The CTA's work is one stream of tile products.  Output tiles are dealt to the CTAs in chunks of `tch`
+    // consecutive tiles (chunk c = blockIdx.x, += gridDim.x): the products of a chunk are one contiguous run of the
+    // pair stream, the sign bit of pair.y ends a tile, so inside a chunk the stream is walked without pair_ptr.
+    // The generator below runs two products ahead of the multiplier, and the pair_ptr bounds of the following chunk
+    // are fetched a whole chunk ahead: no index load is ever waited for.
+    const int64_t nchunks = (nnzb_c + tch - 1) / tch;
+    int64_t g_chunk = blockIdx.x, g_p = 0, g_pend = 0; // generator: chunk, next pair, end of the chunk's pairs
+    int64_t n_chunk = g_chunk + gridDim.x, n_b = 0, n_e = 0;
+    bool g_new = true;
+    auto chunk_bounds = [&](int64_t c, int64_t &b, int64_t &e) {
+        const int64_t t0 = c * tch, t1 = (c + 1) * tch < nnzb_c ? (c + 1) * tch : nnzb_c;
+        b = pair_ptr[t0];
+        e = pair_ptr[t1];
+    };
+    if (g_chunk < nchunks) chunk_bounds(g_chunk, g_p, g_pend); else g_chunk = -1;
+    if (g_chunk >= 0 && n_chunk < nchunks) chunk_bounds(n_chunk, n_b, n_e);
+    auto gen = [&]() -> tc_entry {
+        tc_entry e;
+        e.pr = make_int2(0, 0);
+        e.tb = -2;
+        if (g_chunk < 0) return e;
+        if (g_p >= g_pend) { // the chunk is used up: move to the one whose bounds are already here
+            if (n_chunk >= nchunks) { g_chunk = -1; return e; }
+            g_chunk = n_chunk; g_p = n_b; g_pend = n_e;
+            n_chunk += gridDim.x;
+            if (n_chunk < nchunks) chunk_bounds(n_chunk, n_b, n_e);
+            g_new = true;
+        }
+        e.tb = g_new ? g_chunk * tch : -1;
+        g_new = false;
+        e.pr = pairs[g_p++];
+        return e;
+    };
+
     constexpr int BBLK = (CHUNKS / 4 + 127) / 128; // 4x4 blocks of B per thread (2 for k = 64, 1 for k = 32 on half the threads)
-    uint32_t uses0 = 0, uses1 = 0;                 // commits issued per stage (all threads track them identically)
-    int64_t t = blockIdx.x;
-    int64_t p = 0, p1 = 0;
-    if (t < nnzb_c) { p = pair_ptr[t]; p1 = pair_ptr[t + 1]; }
-    int2 pr_next = make_int2(0, 0);
     float4 breg[BBLK][4];
 
     auto load_a = [&](int s, int ai) {
         const unsigned char *ag = reinterpret_cast<const unsigned char *>(a_vals + (size_t)ai * (K * K));
         const uint32_t a_s = sbase + s * STAGE;
+        // a warp copies 8 rows x 4 chunks: 64 contiguous bytes per row from global memory (full sectors), and every
+        // quarter-warp writes 8 consecutive rows of one chunk column = 128 contiguous bytes of the stage (no bank conflict)
 #pragma unroll
         for (int x = tid; x < CHUNKS; x += 128) {
-            const int row = x / (K / 4), col = x % (K / 4); // chunk `col` of row `row` of the row-major tile
-            cp16(a_s + col * (M * 16) + row * 16, ag + (size_t)x * 16);
+            const int blk = x >> 5, l = x & 31;
+            const int row = 8 * (blk % (K / 8)) + (l & 7), col = 4 * (blk / (K / 8)) + (l >> 3);
+            cp16(a_s + col * (M * 16) + row * 16, ag + (size_t)row * (K * 4) + col * 16);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -156,44 +205,82 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
             if (x < CHUNKS / 4) {
                 const int kq = x / (K / 4), nq = x % (K / 4);
                 float4 *dst = reinterpret_cast<float4 *>(smem + s * STAGE + A_BYTES + kq * (K * 16) + (4 * nq) * 16);
-                dst[0] = make_float4(breg[u][0].x, breg[u][1].x, breg[u][2].x, breg[u][3].x);
-                dst[1] = make_float4(breg[u][0].y, breg[u][1].y, breg[u][2].y, breg[u][3].y);
-                dst[2] = make_float4(breg[u][0].z, breg[u][1].z, breg[u][2].z, breg[u][3].z);
-                dst[3] = make_float4(breg[u][0].w, breg[u][1].w, breg[u][2].w, breg[u][3].w);
+                const float4 o0 = make_float4(breg[u][0].x, breg[u][1].x, breg[u][2].x, breg[u][3].x);
+                const float4 o1 = make_float4(breg[u][0].y, breg[u][1].y, breg[u][2].y, breg[u][3].y);
+                const float4 o2 = make_float4(breg[u][0].z, breg[u][1].z, breg[u][2].z, breg[u][3].z);
+                const float4 o3 = make_float4(breg[u][0].w, breg[u][1].w, breg[u][2].w, breg[u][3].w);
+                // the four chunks of a thread are 64 contiguous bytes, so with a fixed order a quarter-warp would hit two
+                // 16-byte bank groups four times each; starting at chunk (nq / 2) % 4 makes its eight chunks distinct
+                const int rot = (nq >> 1) & 3;
+#pragma unroll
+                for (int tt = 0; tt < 4; tt++) {
+                    const int c = (tt + rot) & 3;
+                    dst[c] = c == 0 ? o0 : (c == 1 ? o1 : (c == 2 ? o2 : o3));
+                }
             }
         }
     };
+    // read accumulator `ab` back and store it as output tile `tile`: the M=64 accumulator layout keeps tile rows
+    // 16w .. 16w+15 in TMEM lanes 32w .. 32w+15, which is what warp w reads with the 16-lane load shape; four lanes then
+    // hold 32 contiguous bytes of a row, so every store instruction writes whole 32-byte sectors with all lanes
+    auto epilogue = [&](int64_t tile, int ab) {
+        float *out = c_vals + (size_t)tile * (K * K) + (size_t)(16 * warp + (lane >> 2)) * K + 2 * (lane & 3);
+        uint32_t v[N / 2];
+        const uint32_t taddr = tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)(ab * N);
+        if constexpr (N == 64) tmem_ld_16x256b_x8(taddr, v); else tmem_ld_16x256b_x4(taddr, v);
+        if (16 * warp < K) {
+#pragma unroll
+            for (int j = 0; j < N / 8; j++) {
+                __stcs(reinterpret_cast<float2 *>(out + 8 * j), make_float2(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1])));
+                __stcs(reinterpret_cast<float2 *>(out + 8 * K + 8 * j),
+                       make_float2(__uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])));
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        // the __syncthreads of a later product orders these TMEM reads before the next MMA into this accumulator
+    };
 
-    if (t < nnzb_c) { // first product: nothing to hide behind
-        const int2 pr = pairs[p];
-        load_a(0, pr.x);
-        load_b(pr.y & 0x7fffffff);
+    // Product i (stage s = i & 1, accumulator ab) goes through:
+    //   0  the B tile of product i+1 is requested into registers (its pair was fetched one product ago)
+    //   1  wait for the A chunks of product i, make this product's stage visible to the tensor core, CTA barrier
+    //   2  one thread issues the MMAs of product i and commits them to the stage's mbarrier
+    //   3  wait for the MMAs of product i-1 (issued a whole product ago): stage s^1 is free, and if i-1 closed its
+    //      tile, that accumulator is complete
+    //   4  the A tile of product i+1 is requested into stage s^1 (cp.async)
+    //   5  if product i-1 closed a tile: read that accumulator back and store the tile -- while product i is multiplied
+    //      into the other accumulator
+    //   6  the B registers are transposed into stage s^1
+    uint32_t uses0 = 0, uses1 = 0; // commits issued per stage (all threads track them identically)
+    tc_entry cur = gen();
+    tc_entry nx1 = gen();
+    int64_t t = cur.tb;
+    int s = 0, ab = 0;
+    bool first_of_tile = true, pend = false;
+    int64_t pend_t = 0;
+    int pend_ab = 0;
+    if (cur.tb != -2) { // first product: nothing to hide behind
+        load_a(0, cur.pr.x);
+        load_b(cur.pr.y & 0x7fffffff);
         store_b(0);
     }
-    int s = 0;
-    bool first_of_tile = true;
-    while (t < nnzb_c) {
-        // the product after this one (same tile, or the first of the CTA's next tile)
-        int64_t tn = t, pn = p + 1, pn1 = p1;
-        if (pn >= p1) {
-            tn = t + gridDim.x;
-            if (tn < nnzb_c) { pn = pair_ptr[tn]; pn1 = pair_ptr[tn + 1]; }
-        }
-        const bool have_next = tn < nnzb_c;
-        const bool last_of_tile = p + 1 >= p1;
-        if (have_next) {
-            const int s1 = s ^ 1;
-            const uint32_t uses = s1 ? uses1 : uses0;
-            if (uses > 0) mbar_wait(bar0 + 8 * s1, (uses - 1) & 1); // the MMAs that read stage s1 are done
-            pr_next = pairs[pn];
-            load_a(s1, pr_next.x);
-            load_b(pr_next.y & 0x7fffffff);
-            asm volatile("cp.async.wait_group 1;" ::: "memory"); // this product's A chunks have landed
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-        }
+    // BSP_F32_PROF=1: cycles thread 0 spends in every step, summed over the CTA's products (prof[8 * blockIdx.x + ...])
+    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tk = 0;
+    auto tick = [&](int slot) {
+        if (PROF && tid == 0) { const long long now = clock64(); pc[slot] += now - tk; tk = now; }
+    };
+    if (PROF && tid == 0) tk = clock64();
+    while (cur.tb != -2) {
+        const bool have_next = nx1.tb != -2;
+        const bool last_of_tile = cur.pr.y < 0;
+        const tc_entry nx2 = gen(); // the pair of product i+2 starts its way here
+        if (have_next) load_b(nx1.pr.y & 0x7fffffff);
+        tick(0);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        tick(1);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy writes -> visible to the tensor core
         __syncthreads();
+        tick(2);
         if (tid == 0) {
             const uint32_t a_s = sbase + s * STAGE, b_s = a_s + A_BYTES;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -207,38 +294,46 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
                     ".reg .pred p;\n\t"
                     "setp.ne.b32 p, %4, 0;\n\t"
                     "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-                    "}" ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+                    "}" ::"r"(tmem + (uint32_t)(ab * N)), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar0 + 8 * s)
                          : "memory");
         }
         if (s) uses1++; else uses0++;
-        if (last_of_tile) {
-            // accumulator complete when this product's commit has arrived (tcgen05 ops retire in order)
-            mbar_wait(bar0 + 8 * s, ((s ? uses1 : uses0) - 1) & 1);
+        tick(3);
+        {
+            const uint32_t uprev = s ? uses0 : uses1; // commits on the other stage: the last one is product i-1's
+            if (uprev > 0) mbar_wait(bar0 + 8 * (s ^ 1), (uprev - 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            // epilogue: TMEM lanes 32w + i (i < 16) hold tile row 16w + i
-            const int row = 16 * warp + lane;
-            const bool valid = lane < 16 && row < K;
-            float *out = c_vals + (size_t)t * (K * K) + (size_t)row * K;
-#pragma unroll
-            for (int c0 = 0; c0 < N; c0 += 16) {
-                float v[16];
-                tmem_ld16(tmem + ((uint32_t)(32 * warp) << 16) + c0, v);
-                if (valid) {
-#pragma unroll
-                    for (int i = 0; i < 16; i += 4)
-                        __stcs(reinterpret_cast<float4 *>(out + c0 + i), make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
-                }
-            }
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            // the next product's __syncthreads orders these TMEM reads before its first MMA
         }
-        if (have_next) store_b(s ^ 1); // the B loads have had the MMA issue and the read-back of the accumulator to hide behind
+        tick(4);
+        if (have_next) load_a(s ^ 1, nx1.pr.x);
+        tick(5);
+        if (pend) {
+            epilogue(pend_t, pend_ab);
+            pend = false;
+        }
+        tick(6);
+        if (have_next) store_b(s ^ 1);
+        tick(7);
+        if (last_of_tile) {
+            pend = true; pend_t = t; pend_ab = ab;
+            ab ^= 1;
+        }
         first_of_tile = last_of_tile;
-        t = tn; p = pn; p1 = pn1;
+        if (have_next) t = nx1.tb >= 0 ? nx1.tb : (last_of_tile ? t + 1 : t);
+        cur = nx1;
+        nx1 = nx2;
         s ^= 1;
     }
+    if (pend) { // the stream's last product closed a tile: its MMAs were committed to stage s^1
+        const uint32_t ulast = s ? uses0 : uses1;
+        mbar_wait(bar0 + 8 * (s ^ 1), (ulast - 1) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        epilogue(pend_t, pend_ab);
+    }
+    if (PROF && tid == 0)
+        for (int i = 0; i < 8; i++) prof[8 * (size_t)blockIdx.x + i] = pc[i];
     __syncthreads();
     if (warp == 0)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
@@ -255,21 +350,54 @@ int bsp_numeric_f32_tc(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const b
         return BSP_ERR_LIMIT;
     }
     const float *a = (const float *)A->vals, *b = (const float *)B->vals;
-    // latency-bound per CTA (load -> MMA -> load ...): fill the SM with as many CTAs as shared memory allows
-    int64_t grid = sym->nnzb_c;
-    const int64_t max_grid = (int64_t)ctx->sm_count * (k == 32 ? 8 : 3);
+    if (sym->nnzb_c == 0) { if (path) *path = 100 + k; return BSP_OK; }
+    const int smem = k == 32 ? 2 * ((32 / 4) * 64 * 16 + (32 / 4) * 32 * 16) : 2 * ((64 / 4) * 64 * 16 + (64 / 4) * 64 * 16);
+    const char *pe = getenv("BSP_F32_PROF"); // per-step cycle counts of thread 0 of every CTA on stderr (diagnosis)
+    const bool profiled = pe && pe[0] == '1';
+    const void *fn = profiled ? (k == 32 ? (const void *)f32_tc_kernel<32, true> : (const void *)f32_tc_kernel<64, true>)
+                              : (k == 32 ? (const void *)f32_tc_kernel<32, false> : (const void *)f32_tc_kernel<64, false>);
+    BSP_CUDA(ctx, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    // one wave: as many CTAs per SM as registers, shared memory and the 512 TMEM columns (2k per CTA) allow.  Worked out
+    // by hand: cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for these kernels on this toolchain, while three
+    // (k = 64) and five (k = 32) CTAs are resident in fact (ncu: sm__warps_active).
+    cudaFuncAttributes fa;
+    BSP_CUDA(ctx, cudaFuncGetAttributes(&fa, fn));
+    const int regs = ((fa.numRegs + 7) / 8) * 8;
+    int per_sm = 65536 / (128 * (regs > 0 ? regs : 8));
+    const int by_smem = (int)((228 * 1024) / ((size_t)smem + fa.sharedSizeBytes + 1024));
+    if (per_sm > by_smem) per_sm = by_smem;
+    if (per_sm > 512 / (2 * k)) per_sm = 512 / (2 * k);
+    if (per_sm < 1) per_sm = 1;
+    const int64_t max_grid = (int64_t)ctx->sm_count * per_sm;
+    // output tiles are dealt in chunks of up to 8 consecutive tiles, fewer when that would leave CTAs without work
+    int tch = (int)(sym->nnzb_c / max_grid);
+    tch = tch < 1 ? 1 : (tch > 8 ? 8 : tch);
+    if (const char *e = getenv("BSP_F32_TCH")) { const int v = atoi(e); if (v >= 1 && v <= 64) tch = v; } // comparison hook
+    int64_t grid = (sym->nnzb_c + tch - 1) / tch;
     if (grid > max_grid) grid = max_grid;
-    if (k == 32) {
-        constexpr int smem = 2 * ((32 / 4) * 64 * 16 + (32 / 4) * 32 * 16);
-        BSP_CUDA(ctx, cudaFuncSetAttribute(f32_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        f32_tc_kernel<32><<<(unsigned)grid, 128, smem, ctx->stream>>>(a, b, sym->pair_ptr, sym->pairs, sym->nnzb_c, c_vals);
-        if (path) *path = 132;
-    } else {
-        constexpr int smem = 2 * ((64 / 4) * 64 * 16 + (64 / 4) * 64 * 16);
-        BSP_CUDA(ctx, cudaFuncSetAttribute(f32_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        f32_tc_kernel<64><<<(unsigned)grid, 128, smem, ctx->stream>>>(a, b, sym->pair_ptr, sym->pairs, sym->nnzb_c, c_vals);
-        if (path) *path = 164;
+    long long *prof = nullptr;
+    if (profiled) {
+        BSP_TRY(bsp_alloc(ctx, &prof, (size_t)grid * 8));
+        BSP_CUDA(ctx, cudaMemsetAsync(prof, 0, (size_t)grid * 8 * sizeof(long long), ctx->stream));
     }
+    {
+        void *args[] = {(void *)&a, (void *)&b, (void *)&sym->pair_ptr, (void *)&sym->pairs, (void *)&sym->nnzb_c, (void *)&tch,
+                        (void *)&c_vals, (void *)&prof};
+        BSP_CUDA(ctx, cudaLaunchKernel(fn, dim3((unsigned)grid), dim3(128), args, (size_t)smem, ctx->stream));
+    }
+    if (prof) {
+        std::vector<long long> h((size_t)grid * 8);
+        BSP_CUDA(ctx, cudaMemcpyAsync(h.data(), prof, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+        BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        bsp_release(ctx, prof);
+        double sum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int64_t c = 0; c < grid; c++) for (int i = 0; i < 8; i++) sum[i] += (double)h[(size_t)c * 8 + i];
+        static const char *names[8] = {"gen+load_b", "wait_a", "fence+sync", "mma_issue", "wait_mma_prev", "load_a", "epilogue", "store_b"};
+        fprintf(stderr, "[bsp f32 prof] k=%d grid=%lld tch=%d per_sm=%d  cycles per product (nprod=%lld):", k, (long long)grid, tch, per_sm, (long long)sym->nprod);
+        for (int i = 0; i < 8; i++) fprintf(stderr, " %s=%.0f", names[i], sum[i] * (double)1 / ((double)sym->nprod));
+        fprintf(stderr, "\n");
+    }
+    if (path) *path = 100 + k;
     BSP_LAUNCH_CHECK(ctx);
     return BSP_OK;
 }

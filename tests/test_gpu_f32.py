@@ -93,3 +93,24 @@ def test_f32_tensor_cores_match_float64_within_tf32(ctx, k):
     # auto picks the tensor-core kernel where it is the faster one (k = 64)
     st = check(ctx, k, 6, 0.5, "auto", 2e-3, seeds=(9, 10))
     assert st.numeric_path == (164 if k == 64 else 100)
+
+
+@pytest.mark.parametrize("k", [32, 64])
+@pytest.mark.parametrize("tch", [1, 3, 8])
+def test_f32_tensor_core_tile_chunks(ctx, k, tch, monkeypatch):
+    """The kernel walks output tiles in chunks of BSP_F32_TCH consecutive tiles (a comparison hook; the
+    library picks 1..8 itself): many pairs per tile, then mostly single-pair tiles with a ragged last chunk."""
+    monkeypatch.setenv("BSP_F32_TCH", str(tch))
+    assert check(ctx, k, 7, 0.6, "tensor", 2e-3, seeds=(11, 12)).numeric_path == 100 + k
+    assert check(ctx, k, 12, 0.08, "tensor", 2e-3, seeds=(13, 14)).numeric_path == 100 + k
+
+
+@pytest.mark.parametrize("k", [32, 64])
+@pytest.mark.parametrize("tch", [0, 1])
+def test_f32_tensor_core_many_tiles(ctx, k, tch, monkeypatch):
+    """More chunks than resident CTAs: every CTA moves through several chunks (0 = the library's own chunk size)."""
+    if tch:
+        monkeypatch.setenv("BSP_F32_TCH", str(tch))
+    else:
+        monkeypatch.delenv("BSP_F32_TCH", raising=False)
+    check(ctx, k, 40, 0.3, "tensor", 2e-3, seeds=(15, 16))
