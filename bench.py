@@ -555,8 +555,13 @@ def run_float(torch, ctx, k, n, density, steps):
             worst = max(worst, float((np.abs(v[t] - ref) / np.maximum(bound, 1e-30)).max()))
         C.free()
         t_ms = sum(ms) / len(ms)
+        # compulsory bytes of the numeric pass: every operand tile once, every output tile once, the pair lists once
+        comp = (a[3].size + b[3].size + int(st.nnzb_c)) * k * k * 4 + 8 * int(st.nprod) + 8 * (int(st.nnzb_c) + 1)
+        peak, peak_src = measured_peak()
         out[path] = {"numeric_ms": t_ms, "numeric_path": st.numeric_path, "gflops": 2.0 * k ** 3 * st.nprod / (t_ms * 1e-3) / 1e9,
-                     "max_err_over_sum_abs": worst}
+                     "max_err_over_sum_abs": worst,
+                     "roofline": {"bound": "hbm", "achieved": comp / (t_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                  "frac": comp / (t_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes": comp, "peak_source": peak_src}}
         out["nprod"], out["nnzb_c"], out["symbolic_ms"] = st.nprod, st.nnzb_c, st.ms_symbolic
     ctx.set_f32_path("auto")
     out["tolerance"] = "tensor (TF32 inputs, fp32 accumulate) <= 2e-3, simt (fp32 FMA) <= 2e-6, relative to sum_j |a_j||b_j|"

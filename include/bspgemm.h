@@ -81,8 +81,8 @@ int bsp_mat_from_coo_f32(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, in
                          const int32_t *brow, const int32_t *bcol, const float *vals, bsp_mat **out);
 int bsp_mat_to_coo_f32(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol, float *vals);
 int bsp_mat_is_f32(const bsp_mat *m);
-/* float32 products: 0 = auto (tensor cores for k = 64, fp32 SIMT otherwise), 1 = fp32 SIMT,
- * 2 = tensor cores (k = 32 or 64) */
+/* float32 products: 0 = auto (tensor cores -- TF32 inputs, fp32 accumulate -- for k = 32 and 64, fp32 SIMT otherwise),
+ * 1 = fp32 SIMT, 2 = tensor cores (k = 32 or 64 only) */
 int bsp_ctx_set_f32_path(bsp_ctx *ctx, int path);
 
 /* Same, from DEVICE memory (arrays are copied, not adopted: the copies are complete on return). */

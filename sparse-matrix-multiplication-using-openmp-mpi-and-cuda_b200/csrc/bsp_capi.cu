@@ -268,6 +268,7 @@ void bsp_ctx_destroy(bsp_ctx *ctx)
     for (int i = 0; i < 32; i++)
         if (ctx->trace_ev[i]) cudaEventDestroy(ctx->trace_ev[i]);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (int i = 0; i < 2; i++) if (ctx->f32_pack[i]) cudaFree(ctx->f32_pack[i]);
     for (int i = 0; i < 2; i++) {
         if (ctx->io_buf[i]) cudaFreeHost(ctx->io_buf[i]);
         if (ctx->io_ev[i]) cudaEventDestroy(ctx->io_ev[i]);

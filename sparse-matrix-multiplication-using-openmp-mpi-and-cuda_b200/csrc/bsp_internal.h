@@ -30,6 +30,8 @@ struct bsp_ctx {
     char *io_buf[2];     // pinned staging pieces of the binary reader/writer, allocated on first use
     cudaEvent_t io_ev[2];
     void *d_counters;    // 256 B of device counters (exact-refold count of the numeric pass)
+    void *f32_pack[2];   // float32 tensor-core path: operands repacked into the instruction's layout (grow-only, bsp_numeric_f32_tc.cu)
+    size_t f32_pack_bytes[2];
     bool force_generic;  // BSP_FORCE_GENERIC=1: always use the any-k exact numeric kernel (tests)
     int f32_path;        // float32 products: 0 = auto (tensor cores for k = 32 / 64), 1 = SIMT, 2 = tensor cores
     int64_t pair_budget; // tile products whose pair lists one symbolic pass may hold (BSP_PAIR_BUDGET); more -> row panels

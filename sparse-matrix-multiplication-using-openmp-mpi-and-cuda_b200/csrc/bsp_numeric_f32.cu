@@ -100,9 +100,9 @@ int bsp_numeric_f32(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const bsp_
     if (sym->nnzb_c == 0) return BSP_OK;
     const int k = A->k;
     const float *a = (const float *)A->vals, *b = (const float *)B->vals;
-    // auto: tensor cores for k = 64 (measured 5.5 ms vs 6.4 ms SIMT on the bench workload); for k = 32 the
-    // M=64 instruction is half empty and the SIMT kernel is faster (7.9 ms vs 11.7 ms), so it needs path = 2
-    if ((ctx->f32_path == 2 && (k == 32 || k == 64)) || (ctx->f32_path == 0 && k == 64)) {
+    // auto: tensor cores for k = 32 and 64 (bench workloads: 4.7 against 7.9 ms SIMT, 2.4 against 6.4 ms); TF32 inputs --
+    // path = 1 keeps fp32 products
+    if ((ctx->f32_path == 2 || ctx->f32_path == 0) && (k == 32 || k == 64)) {
         const int rc = bsp_numeric_f32_tc(ctx, A, B, sym, c_vals, path);
         if (rc != BSP_ERR_LIMIT) return rc;
         if (ctx->f32_path == 2) return rc; // tensor cores were demanded

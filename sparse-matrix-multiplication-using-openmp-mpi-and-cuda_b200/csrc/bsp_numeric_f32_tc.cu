@@ -7,25 +7,20 @@
 // between pairs.
 //
 // One CTA (4 warps) walks a stream of tile products, two shared-memory stages and two TMEM accumulators:
-//   all threads : stage the tiles of product i+1 into stage (i+1)&1 in the canonical no-swizzle K-major
-//                 UMMA layout (8-row x 16-byte core matrices) while product i is multiplied:
-//                   A: element (m, k)  at (k/4)*(64*16) + m*16 + (k%4)*4     LBO = 1024, SBO = 128
-//                      a 16-byte chunk of the row-major tile is already one core-matrix row, so
-//                      A is a pure chunk permutation done by cp.async;
-//                   B: the instruction wants B as N x K with K contiguous, the tile is K x N with
-//                      N contiguous, so each thread transposes 4x4 blocks in registers
-//                      (4 LDG.128 -> 4 STS.128): element (n, k) at (k/4)*(K*16) + n*16 + (k%4)*4
-//                      LBO = K*16, SBO = 128.
+//   repacking   : both operands are first rewritten, tile by tile, into the canonical no-swizzle K-major UMMA layout
+//                 (8-row x 16-byte core matrices), A as it is and B transposed:
+//                   A: element (m, k) at (k/4)*(K*16) + m*16 + (k%4)*4      LBO = K*16, SBO = 128
+//                   B: element (n, k) at (k/4)*(K*16) + n*16 + (k%4)*4      (the instruction wants B as N x K, K contiguous)
 //                 (An MN-major B descriptor would avoid the transpose; with no-swizzle layouts it
 //                 produced zeros in a probe on this toolchain -- tools/scratch/umma_probe.cu.)
-//   one thread  : K/8 tcgen05.mma (M=64, N=K, K=8 each), then tcgen05.commit -> the stage's mbarrier
-//   epilogue    : warp w reads TMEM lanes 32w..32w+15 = tile rows 16w..16w+15 (the M=64
-//                 accumulator layout uses 16 lanes of every sub-partition) and stores them -- one
-//                 product later, while the next tile is multiplied into the other accumulator.
-// The pair of product i+2 and the pair_ptr bounds of the next chunk of tiles are fetched ahead, so the
-// loop waits for no index load (the first version spent ~1.5 of its ~5 us per product there).
-// For k = 32 the M=64 instruction runs with its upper 32 rows unused (the tile product is far
-// below the tensor pipe's rate either way: 8 flop per byte moved).
+//   one thread  : starts the two bulk copies of product i+1 (a packed tile is one contiguous run), waits for those of
+//                 product i on the stage's mbarrier, issues K/8 tcgen05.mma (M=64, N=K, K=8 each) and commits them
+//   all threads : read an accumulator back one product after its tile closed -- while the next tile is multiplied
+//                 into the other accumulator -- with the 16-lane load shape and store it in whole 32-byte sectors.
+// The pair of product i+2 and the pair_ptr bounds of the next chunk of tiles are fetched ahead, so the loop waits for
+// no index load.  For k = 32 the M=64 instruction runs with its upper 32 rows unused.
+// BSP_F32_PROF=1 prints where thread 0 of every CTA spends its cycles (the numbers DESIGN.md section 8 quotes).
+#include <algorithm>
 #include <vector>
 
 #include "bsp_internal.h"
@@ -100,31 +95,72 @@ struct tc_entry {
     int64_t tb;
 };
 
+// ---- operand tiles packed in the UMMA layout ----------------------------------------------------------------------
+// Two small kernels first rewrite the operands tile by tile into the layout the instruction reads (A: [k/4][m] 16-byte
+// chunks; B: transposed, [k/4][n] chunks), so that a tile is one contiguous run of 4*K*K bytes and ONE thread fetches it
+// with a single cp.async.bulk that signals the stage's mbarrier.  (The version before this one staged the tiles with all
+// threads -- 16 LDGSTS/LDG and 8 STS per thread and product, B transposed in registers: 3.66 ms on the k = 64 bench
+// workload against 2.15 ms + 0.23 ms of repacking here; the bytes an SM keeps in flight through its load/store unit
+// were the limit, more resident CTAs only made each one slower.)
+
+template <int K>
+__global__ void __launch_bounds__(256)
+f32_pack_a_kernel(const float4 *__restrict__ src, float4 *__restrict__ dst, int64_t nchunks_total)
+{
+    constexpr int CH = K * K / 4; // 16-byte chunks per tile
+    for (int64_t g = (int64_t)blockIdx.x * 256 + threadIdx.x; g < nchunks_total; g += (int64_t)gridDim.x * 256) {
+        const int64_t tile = g / CH;
+        const int o = (int)(g % CH);   // output chunk: kc * K + m
+        const int kc = o / K, m = o % K;
+        dst[g] = src[tile * CH + m * (K / 4) + kc]; // rows of one tile stay in L1 between the K/4 passes over them
+    }
+}
+
+template <int K>
+__global__ void __launch_bounds__(256)
+f32_pack_b_kernel(const float *__restrict__ src, float4 *__restrict__ dst, int64_t nchunks_total)
+{
+    constexpr int CH = K * K / 4;
+    for (int64_t g = (int64_t)blockIdx.x * 256 + threadIdx.x; g < nchunks_total; g += (int64_t)gridDim.x * 256) {
+        const int64_t tile = g / CH;
+        const int o = (int)(g % CH);   // output chunk: kc * K + n  =  B[4kc .. 4kc+3][n]
+        const int kc = o / K, n = o % K;
+        const float *s = src + tile * (K * K) + (size_t)(4 * kc) * K + n;
+        dst[g] = make_float4(s[0], s[K], s[2 * K], s[3 * K]);
+    }
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
 template <int K, bool PROF>
 __global__ void __launch_bounds__(128)
-f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals, const int64_t *__restrict__ pair_ptr,
-              const int2 *__restrict__ pairs, int64_t nnzb_c, int tch, float *__restrict__ c_vals, long long *__restrict__ prof)
+f32_tcb_kernel(const float *__restrict__ a_pack, const float *__restrict__ b_pack, const int64_t *__restrict__ pair_ptr,
+               const int2 *__restrict__ pairs, int64_t nnzb_c, int tch, float *__restrict__ c_vals, long long *__restrict__ prof)
 {
     constexpr int M = 64, N = K;
-    constexpr int A_BYTES = (K / 4) * M * 16;  // chunk-major A: [kc][m] 16-byte chunks (64 rows, K=32 uses 32)
-    constexpr int B_BYTES = (K / 4) * N * 16;  // chunk-major B^T: [kc][n] 16-byte chunks
-    constexpr int STAGE = A_BYTES + B_BYTES;
-    constexpr int CHUNKS = K * K / 4;          // 16-byte chunks per tile
-    constexpr int TMEM_COLS = 2 * N;           // two accumulators: one is read back while the next tile is multiplied
+    constexpr int TILE = K * K * 4;   // bytes of one packed tile
+    constexpr int STAGE = 2 * TILE;   // A then B.  k = 32: the M=64 instruction reads 32 rows past the A tile's, i.e. the
+                                      // next chunk column or the head of B -- finite values in accumulator rows nobody reads
+    constexpr int TMEM_COLS = 2 * N;
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) uint64_t mbar[2];
+    __shared__ __align__(8) uint64_t mbar[4]; // [0..1] stage filled (bulk copies landed), [2..3] stage's MMAs retired
     __shared__ uint32_t tmem_base_sh;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t sbase = smem_u32(smem);
-    const uint32_t bar0 = smem_u32(&mbar[0]);
+    const uint32_t barf = smem_u32(&mbar[0]), bard = smem_u32(&mbar[2]);
 
     if (tid == 0) {
-        mbar_init(bar0, 1);
-        mbar_init(bar0 + 8, 1);
+        for (int i = 0; i < 4; i++) mbar_init(barf + 8 * i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (K == 32) // rows 32..63 of the A stages are never written: clear them once so they hold finite values
-        for (int i = tid; i < 2 * STAGE / 16; i += 128) reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0, 0, 0, 0);
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_sh)),
                      "n"(TMEM_COLS) : "memory");
@@ -142,7 +178,7 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
     // The generator below runs two products ahead of the multiplier, and the pair_ptr bounds of the following chunk
     // are fetched a whole chunk ahead: no index load is ever waited for.
     const int64_t nchunks = (nnzb_c + tch - 1) / tch;
-    int64_t g_chunk = blockIdx.x, g_p = 0, g_pend = 0; // generator: chunk, next pair, end of the chunk's pairs
+    int64_t g_chunk = blockIdx.x, g_p = 0, g_pend = 0;
     int64_t n_chunk = g_chunk + gridDim.x, n_b = 0, n_e = 0;
     bool g_new = true;
     auto chunk_bounds = [&](int64_t c, int64_t &b, int64_t &e) {
@@ -157,7 +193,7 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
         e.pr = make_int2(0, 0);
         e.tb = -2;
         if (g_chunk < 0) return e;
-        if (g_p >= g_pend) { // the chunk is used up: move to the one whose bounds are already here
+        if (g_p >= g_pend) {
             if (n_chunk >= nchunks) { g_chunk = -1; return e; }
             g_chunk = n_chunk; g_p = n_b; g_pend = n_e;
             n_chunk += gridDim.x;
@@ -170,55 +206,11 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
         return e;
     };
 
-    constexpr int BBLK = (CHUNKS / 4 + 127) / 128; // 4x4 blocks of B per thread (2 for k = 64, 1 for k = 32 on half the threads)
-    float4 breg[BBLK][4];
-
-    auto load_a = [&](int s, int ai) {
-        const unsigned char *ag = reinterpret_cast<const unsigned char *>(a_vals + (size_t)ai * (K * K));
-        const uint32_t a_s = sbase + s * STAGE;
-        // a warp copies 8 rows x 4 chunks: 64 contiguous bytes per row from global memory (full sectors), and every
-        // quarter-warp writes 8 consecutive rows of one chunk column = 128 contiguous bytes of the stage (no bank conflict)
-#pragma unroll
-        for (int x = tid; x < CHUNKS; x += 128) {
-            const int blk = x >> 5, l = x & 31;
-            const int row = 8 * (blk % (K / 8)) + (l & 7), col = 4 * (blk / (K / 8)) + (l >> 3);
-            cp16(a_s + col * (M * 16) + row * 16, ag + (size_t)row * (K * 4) + col * 16);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    auto load_b = [&](int bi) {
-        const float *bg = b_vals + (size_t)bi * (K * K);
-#pragma unroll
-        for (int u = 0; u < BBLK; u++) {
-            const int x = tid + 128 * u;
-            if (x < CHUNKS / 4) {
-                const int kq = x / (K / 4), nq = x % (K / 4);
-#pragma unroll
-                for (int r = 0; r < 4; r++) breg[u][r] = *reinterpret_cast<const float4 *>(bg + (size_t)(4 * kq + r) * K + 4 * nq);
-            }
-        }
-    };
-    auto store_b = [&](int s) { // 4x4 blocks transposed in registers: element (n, k) at (k/4)*(K*16) + n*16 + (k%4)*4
-#pragma unroll
-        for (int u = 0; u < BBLK; u++) {
-            const int x = tid + 128 * u;
-            if (x < CHUNKS / 4) {
-                const int kq = x / (K / 4), nq = x % (K / 4);
-                float4 *dst = reinterpret_cast<float4 *>(smem + s * STAGE + A_BYTES + kq * (K * 16) + (4 * nq) * 16);
-                const float4 o0 = make_float4(breg[u][0].x, breg[u][1].x, breg[u][2].x, breg[u][3].x);
-                const float4 o1 = make_float4(breg[u][0].y, breg[u][1].y, breg[u][2].y, breg[u][3].y);
-                const float4 o2 = make_float4(breg[u][0].z, breg[u][1].z, breg[u][2].z, breg[u][3].z);
-                const float4 o3 = make_float4(breg[u][0].w, breg[u][1].w, breg[u][2].w, breg[u][3].w);
-                // the four chunks of a thread are 64 contiguous bytes, so with a fixed order a quarter-warp would hit two
-                // 16-byte bank groups four times each; starting at chunk (nq / 2) % 4 makes its eight chunks distinct
-                const int rot = (nq >> 1) & 3;
-#pragma unroll
-                for (int tt = 0; tt < 4; tt++) {
-                    const int c = (tt + rot) & 3;
-                    dst[c] = c == 0 ? o0 : (c == 1 ? o1 : (c == 2 ? o2 : o3));
-                }
-            }
-        }
+    auto fill = [&](int st, const int2 pr) { // one thread: both tiles of a product into stage st
+        const uint32_t fb = barf + 8 * st, dst = sbase + st * STAGE;
+        mbar_expect_tx(fb, 2 * TILE);
+        bulk_g2s(dst, a_pack + (size_t)pr.x * (K * K), TILE, fb);
+        bulk_g2s(dst + TILE, b_pack + (size_t)(pr.y & 0x7fffffff) * (K * K), TILE, fb);
     };
     // read accumulator `ab` back and store it as output tile `tile`: the M=64 accumulator layout keeps tile rows
     // 16w .. 16w+15 in TMEM lanes 32w .. 32w+15, which is what warp w reads with the 16-lane load shape; four lanes then
@@ -237,20 +229,15 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
             }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        // the __syncthreads of a later product orders these TMEM reads before the next MMA into this accumulator
     };
 
-    // Product i (stage s = i & 1, accumulator ab) goes through:
-    //   0  the B tile of product i+1 is requested into registers (its pair was fetched one product ago)
-    //   1  wait for the A chunks of product i, make this product's stage visible to the tensor core, CTA barrier
-    //   2  one thread issues the MMAs of product i and commits them to the stage's mbarrier
-    //   3  wait for the MMAs of product i-1 (issued a whole product ago): stage s^1 is free, and if i-1 closed its
-    //      tile, that accumulator is complete
-    //   4  the A tile of product i+1 is requested into stage s^1 (cp.async)
-    //   5  if product i-1 closed a tile: read that accumulator back and store the tile -- while product i is multiplied
-    //      into the other accumulator
-    //   6  the B registers are transposed into stage s^1
-    uint32_t uses0 = 0, uses1 = 0; // commits issued per stage (all threads track them identically)
+    // Product i (stage s = i & 1, accumulator ab):
+    //   1  CTA barrier (orders the last read-back before MMAs into that accumulator)
+    //   2  one thread waits for the stage's bulk copies, issues the MMAs of product i and commits them
+    //   3  all wait for the MMAs of product i-1: stage s^1 is free, the accumulator of a tile closed by i-1 is complete
+    //   4  one thread starts the bulk copies of product i+1 into stage s^1
+    //   5  if product i-1 closed a tile: read it back and store it, while product i is multiplied
+    uint32_t uses0 = 0, uses1 = 0, fills0 = 0, fills1 = 0;
     tc_entry cur = gen();
     tc_entry nx1 = gen();
     int64_t t = cur.tb;
@@ -258,12 +245,10 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
     bool first_of_tile = true, pend = false;
     int64_t pend_t = 0;
     int pend_ab = 0;
-    if (cur.tb != -2) { // first product: nothing to hide behind
-        load_a(0, cur.pr.x);
-        load_b(cur.pr.y & 0x7fffffff);
-        store_b(0);
+    if (cur.tb != -2) {
+        if (tid == 0) fill(0, cur.pr);
+        fills0++;
     }
-    // BSP_F32_PROF=1: cycles thread 0 spends in every step, summed over the CTA's products (prof[8 * blockIdx.x + ...])
     long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long tk = 0;
     auto tick = [&](int slot) {
@@ -273,20 +258,18 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
     while (cur.tb != -2) {
         const bool have_next = nx1.tb != -2;
         const bool last_of_tile = cur.pr.y < 0;
-        const tc_entry nx2 = gen(); // the pair of product i+2 starts its way here
-        if (have_next) load_b(nx1.pr.y & 0x7fffffff);
+        const tc_entry nx2 = gen();
         tick(0);
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        tick(1);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy writes -> visible to the tensor core
         __syncthreads();
-        tick(2);
+        tick(1);
         if (tid == 0) {
-            const uint32_t a_s = sbase + s * STAGE, b_s = a_s + A_BYTES;
+            mbar_wait(barf + 8 * s, ((s ? fills1 : fills0) - 1) & 1);
+            if (PROF) tick(2);
+            const uint32_t a_s = sbase + s * STAGE, b_s = a_s + TILE;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
             for (int ks = 0; ks < K / 8; ks++) {
-                const uint64_t da = umma_desc(a_s + ks * 2 * (M * 16), M * 16, 128);
+                const uint64_t da = umma_desc(a_s + ks * 2 * (K * 16), K * 16, 128);
                 const uint64_t db = umma_desc(b_s + ks * 2 * (K * 16), K * 16, 128);
                 const uint32_t accumulate = (!first_of_tile || ks > 0) ? 1u : 0u;
                 asm volatile(
@@ -296,26 +279,27 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
                     "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
                     "}" ::"r"(tmem + (uint32_t)(ab * N)), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
             }
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar0 + 8 * s)
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bard + 8 * s)
                          : "memory");
         }
         if (s) uses1++; else uses0++;
         tick(3);
         {
-            const uint32_t uprev = s ? uses0 : uses1; // commits on the other stage: the last one is product i-1's
-            if (uprev > 0) mbar_wait(bar0 + 8 * (s ^ 1), (uprev - 1) & 1);
+            const uint32_t uprev = s ? uses0 : uses1;
+            if (uprev > 0) mbar_wait(bard + 8 * (s ^ 1), (uprev - 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
         tick(4);
-        if (have_next) load_a(s ^ 1, nx1.pr.x);
+        if (have_next) {
+            if (tid == 0) fill(s ^ 1, nx1.pr);
+            if (s) fills0++; else fills1++;
+        }
         tick(5);
         if (pend) {
             epilogue(pend_t, pend_ab);
             pend = false;
         }
         tick(6);
-        if (have_next) store_b(s ^ 1);
-        tick(7);
         if (last_of_tile) {
             pend = true; pend_t = t; pend_ab = ab;
             ab ^= 1;
@@ -326,9 +310,9 @@ f32_tc_kernel(const float *__restrict__ a_vals, const float *__restrict__ b_vals
         nx1 = nx2;
         s ^= 1;
     }
-    if (pend) { // the stream's last product closed a tile: its MMAs were committed to stage s^1
+    if (pend) {
         const uint32_t ulast = s ? uses0 : uses1;
-        mbar_wait(bar0 + 8 * (s ^ 1), (ulast - 1) & 1);
+        mbar_wait(bard + 8 * (s ^ 1), (ulast - 1) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         epilogue(pend_t, pend_ab);
     }
@@ -351,12 +335,42 @@ int bsp_numeric_f32_tc(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const b
     }
     const float *a = (const float *)A->vals, *b = (const float *)B->vals;
     if (sym->nnzb_c == 0) { if (path) *path = 100 + k; return BSP_OK; }
-    const int smem = k == 32 ? 2 * ((32 / 4) * 64 * 16 + (32 / 4) * 32 * 16) : 2 * ((64 / 4) * 64 * 16 + (64 / 4) * 64 * 16);
+    const int smem = 4 * k * k * 4; // two stages of (A tile, B tile)
     const char *pe = getenv("BSP_F32_PROF"); // per-step cycle counts of thread 0 of every CTA on stderr (diagnosis)
     const bool profiled = pe && pe[0] == '1';
-    const void *fn = profiled ? (k == 32 ? (const void *)f32_tc_kernel<32, true> : (const void *)f32_tc_kernel<64, true>)
-                              : (k == 32 ? (const void *)f32_tc_kernel<32, false> : (const void *)f32_tc_kernel<64, false>);
+    const void *fn = profiled ? (k == 32 ? (const void *)f32_tcb_kernel<32, true> : (const void *)f32_tcb_kernel<64, true>)
+                              : (k == 32 ? (const void *)f32_tcb_kernel<32, false> : (const void *)f32_tcb_kernel<64, false>);
     BSP_CUDA(ctx, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    { // operands rewritten tile by tile into the layout the instruction reads
+        // the two buffers live on the context and only grow: taking 2 x 344 MB from the stream-ordered pool cost 3.4 ms of
+        // idle GPU per product on the bench workload, thirty times the repacking itself
+        const size_t need[2] = {(size_t)A->nnzb * k * k * sizeof(float), (size_t)B->nnzb * k * k * sizeof(float)};
+        for (int i = 0; i < 2; i++) {
+            if (ctx->f32_pack_bytes[i] >= need[i]) continue;
+            BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); // earlier products may still read the old buffer
+            if (ctx->f32_pack[i]) cudaFree(ctx->f32_pack[i]);
+            ctx->f32_pack[i] = nullptr;
+            ctx->f32_pack_bytes[i] = 0;
+            const size_t bytes = need[i] + need[i] / 8 + 256;
+            BSP_CUDA(ctx, cudaMalloc(&ctx->f32_pack[i], bytes));
+            ctx->f32_pack_bytes[i] = bytes;
+        }
+        float *ap = (float *)ctx->f32_pack[0], *bp = (float *)ctx->f32_pack[1];
+        const int64_t ca = A->nnzb * (int64_t)(k * k / 4), cb = B->nnzb * (int64_t)(k * k / 4);
+        const int64_t cap = (int64_t)ctx->sm_count * 32;
+        const unsigned ga = (unsigned)std::min<int64_t>((ca + 255) / 256, cap), gb = (unsigned)std::min<int64_t>((cb + 255) / 256, cap);
+        if (k == 32) {
+            if (ca) f32_pack_a_kernel<32><<<ga, 256, 0, ctx->stream>>>((const float4 *)a, (float4 *)ap, ca);
+            if (cb) f32_pack_b_kernel<32><<<gb, 256, 0, ctx->stream>>>(b, (float4 *)bp, cb);
+        } else {
+            if (ca) f32_pack_a_kernel<64><<<ga, 256, 0, ctx->stream>>>((const float4 *)a, (float4 *)ap, ca);
+            if (cb) f32_pack_b_kernel<64><<<gb, 256, 0, ctx->stream>>>(b, (float4 *)bp, cb);
+        }
+        BSP_LAUNCH_CHECK(ctx);
+        ctx->launches++;
+        bsp_trace_mark(ctx, "f32_pack");
+        a = ap; b = bp;
+    }
     // one wave: as many CTAs per SM as registers, shared memory and the 512 TMEM columns (2k per CTA) allow.  Worked out
     // by hand: cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for these kernels on this toolchain, while three
     // (k = 64) and five (k = 32) CTAs are resident in fact (ncu: sm__warps_active).
@@ -392,7 +406,7 @@ int bsp_numeric_f32_tc(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, const b
         bsp_release(ctx, prof);
         double sum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         for (int64_t c = 0; c < grid; c++) for (int i = 0; i < 8; i++) sum[i] += (double)h[(size_t)c * 8 + i];
-        static const char *names[8] = {"gen+load_b", "wait_a", "fence+sync", "mma_issue", "wait_mma_prev", "load_a", "epilogue", "store_b"};
+        static const char *names[8] = {"generator", "cta_barrier", "wait_copies", "mma_issue", "wait_mma_prev", "start_copies", "read_back", "-"};
         fprintf(stderr, "[bsp f32 prof] k=%d grid=%lld tch=%d per_sm=%d  cycles per product (nprod=%lld):", k, (long long)grid, tch, per_sm, (long long)sym->nprod);
         for (int i = 0; i < 8; i++) fprintf(stderr, " %s=%.0f", names[i], sum[i] * (double)1 / ((double)sym->nprod));
         fprintf(stderr, "\n");
