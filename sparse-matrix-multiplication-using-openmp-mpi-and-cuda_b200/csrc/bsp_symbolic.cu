@@ -232,20 +232,19 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
 {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ int sm33[33];
-    uint32_t *bm = smem;
-    uint32_t *wrank = bm + words;
-    int2 *aent = (int2 *)(wrank + words);                        // [acap+2] (first B tile, product offset) per A entry
+    uint2 *bmr = (uint2 *)smem;                                  // [words] .x = bitmap word of the row's block columns, .y = its rank
+    int2 *aent = (int2 *)(bmr + words);                          // [acap+2] (first B tile, product offset) per A entry
     int *cur = (int *)(aent + acap + 2);                         // [tcap+4] per-tile counter, then cursor
     int2 *sp = (int2 *)(cur + tcap + 4);                         // [pcap]   the row's pairs
     unsigned short *prodt = (unsigned short *)(sp + pcap);       // [pcap+8] output tile (rank in the row) of every product
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = threadIdx.x & 31;
     const int row = rowlist[blockIdx.x];
     const int cbase = c_rowptr[row], T = c_rowptr[row + 1] - cbase;
     const int64_t pbase = row_prod_ptr[row];
     const int P = (int)(row_prod_ptr[row + 1] - pbase);
     const int a0 = a_rowptr[row], nA = a_rowptr[row + 1] - a0;
 
-    for (int w = tid; w < words; w += FILL_THREADS) bm[w] = 0u;
+    for (int w = tid; w < words; w += FILL_THREADS) bmr[w] = make_uint2(0u, 0u);
     for (int t = tid; t < T + 1; t += FILL_THREADS) cur[t] = 0;
     // 0. A entries: first tile of B row j and (after the scan) the offset of its products
     int carry = 0;
@@ -306,7 +305,7 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
             for (int u = 0; u < UB; u++)
                 if (addr[u] >= 0) {
                     tmpc[xb + u] = cv[u];
-                    atomicOr(&bm[cv[u] >> 5], 1u << (cv[u] & 31));
+                    atomicOr(&bmr[cv[u] >> 5].x, 1u << (cv[u] & 31));
                 }
         }
     }
@@ -315,11 +314,11 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     carry = 0;
     for (int w0 = 0; w0 < words; w0 += FILL_THREADS) {
         const int w = w0 + tid;
-        const uint32_t bits = w < words ? bm[w] : 0u;
+        const uint32_t bits = w < words ? bmr[w].x : 0u;
         int tot;
         const int ex = block_excl_scan_i32(__popc(bits), sm33, &tot);
         if (w < words) {
-            wrank[w] = (uint32_t)(carry + ex);
+            bmr[w].y = (uint32_t)(carry + ex);
             uint32_t b = bits;
             int o = carry + ex;
             while (b) {
@@ -335,7 +334,8 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     // 3. output tile of every product (16-bit rank in the row) + pairs per tile
     for (int x = x0; x < x1; x++) {
         const int c = tmpc[x];
-        const int t = (int)wrank[c >> 5] + __popc(bm[c >> 5] & ((1u << (c & 31)) - 1u));
+        const uint2 br = bmr[c >> 5]; // bitmap word and its rank in one 8-byte read
+        const int t = (int)br.y + __popc(br.x & ((1u << (c & 31)) - 1u));
         prodt[x] = (unsigned short)t;
         atomicAdd(&cur[t], 1);
     }
@@ -359,6 +359,7 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         // 5a. every tile has few pairs: place all products at once (cursor bumped atomically, any
         //     order), then put each tile's pairs in ascending A index -- which is ascending j,
         //     because the A row is sorted -- with a tiny insertion sort, one thread per tile.
+        if (tid == 0) sm33[0] = 0; // length of the sort work list (published by the barrier after the placement)
         {
             int e = e_run;
             int2 ae = aent[e];
@@ -370,15 +371,45 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
             }
         }
         __syncthreads();
-        for (int t = tid; t < T; t += FILL_THREADS) {
-            const int e1 = cur[t], s1 = t ? cur[t - 1] : 0; // cursors now hold tile ends
+        // One pair: nothing to order.  Two pairs: one compare.  Three or more (about one tile in ten on a uniform
+        // 1 % pattern): the tile goes on a work list -- the product-tile table is free now -- so that the insertion sorts
+        // run on full warps afterwards instead of on a few lanes of every warp.
+        unsigned short *work = prodt;
+        for (int t0 = 0; t0 < T; t0 += FILL_THREADS) {
+            const int t = t0 + tid;
+            int cnt = 0, s1 = 0;
+            if (t < T) {
+                s1 = t ? cur[t - 1] : 0; // cursors now hold tile ends
+                cnt = cur[t] - s1;
+            }
+            if (cnt == 1) {
+                sp[s1].y |= (int)0x80000000; // 6. last pair of the tile
+            } else if (cnt == 2) {
+                int2 p0 = sp[s1], p1 = sp[s1 + 1];
+                if (p0.x > p1.x) { const int2 sw = p0; p0 = p1; p1 = sw; sp[s1] = p0; }
+                p1.y |= (int)0x80000000;
+                sp[s1 + 1] = p1;
+            }
+            const unsigned many = __ballot_sync(0xffffffffu, cnt > 2);
+            if (many) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&sm33[0], __popc(many));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (cnt > 2) work[base + __popc(many & ((1u << lane) - 1u))] = (unsigned short)t;
+            }
+        }
+        __syncthreads();
+        const int nwork = sm33[0];
+        for (int w = tid; w < nwork; w += FILL_THREADS) {
+            const int t = work[w];
+            const int e1 = cur[t], s1 = t ? cur[t - 1] : 0;
             for (int i = s1 + 1; i < e1; i++) {
                 const int2 v = sp[i];
                 int j = i - 1;
                 while (j >= s1 && sp[j].x > v.x) { sp[j + 1] = sp[j]; j--; }
                 sp[j + 1] = v;
             }
-            sp[e1 - 1].y |= (int)0x80000000; // 6. last pair of the tile
+            sp[e1 - 1].y |= (int)0x80000000;
         }
         __syncthreads();
     } else {
