@@ -180,7 +180,7 @@ sym_count_heavy_kernel(const int32_t *__restrict__ heavy_list, const int32_t *__
 
 // ---- fill, shared-memory variant: one CTA per block row of C ----------------------------------
 // Everything the row needs lives in shared memory: the column bitmap and its rank table, one
-// counter per output tile, and the row's whole pair list (8 B per tile product).  Pairs are
+// counter per output tile, and the row's whole pair list (4 B per tile product, packed).  Pairs are
 // placed in ascending j by walking the A row entry by entry with the whole CTA spread over
 // B row j (inside one j every target tile is distinct, so the cursor bump needs no atomic),
 // then streamed to global memory with coalesced stores -- DRAM sees each pair exactly once.
@@ -217,12 +217,23 @@ __device__ __forceinline__ int block_excl_scan_i32(int v, int *sm33, int *total)
 }
 
 // Shared-memory budget of one row: 8*words (bitmap + rank table) + 8*(acap+2) (A entries)
-// + 4*(tcap+4) (tile counters) + 8*pcap (the row's pairs) + 2*(pcap+8) (tile of every product).
+// + 4*(tcap+4) (tile counters) + 4*pcap (the row's pairs, packed) + 2*(pcap+8) (tile of every product).
 __host__ __device__ inline size_t fill_smem_bytes(int words, int pcap, int tcap, int acap)
 {
-    return 8 * (size_t)words + 8 * ((size_t)acap + 2) + 4 * ((size_t)tcap + 4) + 8 * (size_t)pcap + 2 * ((size_t)pcap + 8);
+    return 8 * (size_t)words + 8 * ((size_t)acap + 2) + 4 * ((size_t)tcap + 4) + 4 * (size_t)pcap + 2 * ((size_t)pcap + 8);
 }
 
+// A pair is kept in shared memory as one word: bit 31 = last pair of its tile, bits 22..30 = ordinal of the A entry
+// in the row (below FILL_ACAP), bits 0..21 = offset of the B tile in its block row.  Half the bytes of the (A tile,
+// B tile) index pair that goes to global memory -- a third more rows per SM -- and the word orders a tile's pairs
+// by A entry as it is.  Block rows of B longer than 2^22 tiles keep the row out of this kernel (bsp_symbolic).
+constexpr int FILL_ACAP = 512;
+constexpr int FILL_IBITS = 22;
+
+// BSP_SYM_PROF=1: cycles thread 0 of every CTA spends in each phase of sym_fill_smem_kernel (summed over rows)
+__device__ unsigned long long sym_fill_prof[8];
+
+template <bool PROF>
 __global__ void __launch_bounds__(FILL_THREADS)
 sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restrict__ a_rowptr,
                      const int32_t *__restrict__ a_colidx, int b_nbr, const int32_t *__restrict__ b_rowptr,
@@ -235,7 +246,7 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     uint2 *bmr = (uint2 *)smem;                                  // [words] .x = bitmap word of the row's block columns, .y = its rank
     int2 *aent = (int2 *)(bmr + words);                          // [acap+2] (first B tile, product offset) per A entry
     int *cur = (int *)(aent + acap + 2);                         // [tcap+4] per-tile counter, then cursor
-    int2 *sp = (int2 *)(cur + tcap + 4);                         // [pcap]   the row's pairs
+    uint32_t *sp = (uint32_t *)(cur + tcap + 4);                 // [pcap]   the row's pairs, packed
     unsigned short *prodt = (unsigned short *)(sp + pcap);       // [pcap+8] output tile (rank in the row) of every product
     const int tid = threadIdx.x, lane = threadIdx.x & 31;
     const int row = rowlist[blockIdx.x];
@@ -244,6 +255,11 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     const int P = (int)(row_prod_ptr[row + 1] - pbase);
     const int a0 = a_rowptr[row], nA = a_rowptr[row + 1] - a0;
 
+    long long tk = 0;
+    auto tick = [&](int slot) {
+        if (PROF && tid == 0) { const long long now = clock64(); atomicAdd(&sym_fill_prof[slot], (unsigned long long)(now - tk)); tk = now; }
+    };
+    if (PROF && tid == 0) tk = clock64();
     for (int w = tid; w < words; w += FILL_THREADS) bmr[w] = make_uint2(0u, 0u);
     for (int t = tid; t < T + 1; t += FILL_THREADS) cur[t] = 0;
     // 0. A entries: first tile of B row j and (after the scan) the offset of its products
@@ -262,11 +278,11 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
     }
     if (tid == 0) aent[nA] = make_int2(0, P);
     __syncthreads();
+    tick(0);
     // 1. one pass over the row's products, flattened over the CTA (x = product number): find
     //    its A entry by binary search in the offset table, read its block column from B once,
     //    keep it in shared memory (in the area the pairs will occupy later) and set its bit
     int *tmpc = (int *)sp;
-    int *scol = tmpc + pcap; // [T <= pcap] sorted block columns of the C row, staged for a coalesced store
     // every thread owns a contiguous run of products [x0, x1): one binary search for the A entry
     // of x0, then it walks forward (runs are ~P/512 long, so consecutive lanes read consecutive
     // memory and the run length being odd keeps the shared-memory stores conflict-free)
@@ -310,7 +326,9 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         }
     }
     __syncthreads();
-    // 2. rank table + sorted colidx of the C row
+    tick(1);
+    // 2. rank table; the sorted block columns of the C row go straight to global memory (a thread writes the
+    //    columns of its bitmap word to consecutive slots, neighbouring threads to neighbouring runs)
     carry = 0;
     for (int w0 = 0; w0 < words; w0 += FILL_THREADS) {
         const int w = w0 + tid;
@@ -320,17 +338,17 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         if (w < words) {
             bmr[w].y = (uint32_t)(carry + ex);
             uint32_t b = bits;
-            int o = carry + ex;
+            int32_t *o = c_colidx + cbase + carry + ex;
             while (b) {
                 const int bit = __ffs(b) - 1;
                 b &= b - 1;
-                scol[o++] = w * 32 + bit;
+                *o++ = w * 32 + bit;
             }
         }
         carry += tot;
     }
     __syncthreads();
-    for (int t = tid; t < T; t += FILL_THREADS) c_colidx[cbase + t] = scol[t];
+    tick(2);
     // 3. output tile of every product (16-bit rank in the row) + pairs per tile
     for (int x = x0; x < x1; x++) {
         const int c = tmpc[x];
@@ -340,6 +358,7 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         atomicAdd(&cur[t], 1);
     }
     __syncthreads();
+    tick(3);
     // 4. exclusive scan -> first slot of every tile; publish pair_ptr; cur[] becomes the cursor
     //    (every thread scans a contiguous chunk of tiles serially; one block scan joins the chunks)
     int maxcnt = 0;
@@ -355,10 +374,12 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
         for (int t = tid; t < T; t += FILL_THREADS) pair_ptr[(size_t)cbase + t] = pbase + cur[t];
     }
     maxcnt = __syncthreads_or(maxcnt > FILL_SORT_MAX);
+    tick(4);
+    constexpr uint32_t LAST = 0x80000000u;
     if (!maxcnt) {
         // 5a. every tile has few pairs: place all products at once (cursor bumped atomically, any
-        //     order), then put each tile's pairs in ascending A index -- which is ascending j,
-        //     because the A row is sorted -- with a tiny insertion sort, one thread per tile.
+        //     order), then put each tile's pairs in ascending A entry -- which is ascending j,
+        //     because the A row is sorted.
         if (tid == 0) sm33[0] = 0; // length of the sort work list (published by the barrier after the placement)
         {
             int e = e_run;
@@ -367,13 +388,15 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
             for (int x = x0; x < x1; x++) {
                 while (x >= next_off) { e++; ae = aent[e]; next_off = aent[e + 1].y; }
                 const int pos = atomicAdd(&cur[prodt[x]], 1);
-                sp[pos] = make_int2(a0 + e, ae.x + (x - ae.y));
+                sp[pos] = ((uint32_t)e << FILL_IBITS) | (uint32_t)(x - ae.y);
             }
         }
         __syncthreads();
-        // One pair: nothing to order.  Two pairs: one compare.  Three or more (about one tile in ten on a uniform
-        // 1 % pattern): the tile goes on a work list -- the product-tile table is free now -- so that the insertion sorts
-        // run on full warps afterwards instead of on a few lanes of every warp.
+        tick(5);
+        // One pair: nothing to order.  Two pairs: one compare.  Both without a branch: first and last pair of the
+        // tile are read, put in order and written back with the flag on the last.  Three or more (about one tile in ten
+        // on a uniform 1 % pattern): the tile goes on a work list -- the product-tile table is free now -- so that the
+        // insertion sorts run on full warps afterwards instead of on a few lanes of every warp.
         unsigned short *work = prodt;
         for (int t0 = 0; t0 < T; t0 += FILL_THREADS) {
             const int t = t0 + tid;
@@ -382,13 +405,10 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
                 s1 = t ? cur[t - 1] : 0; // cursors now hold tile ends
                 cnt = cur[t] - s1;
             }
-            if (cnt == 1) {
-                sp[s1].y |= (int)0x80000000; // 6. last pair of the tile
-            } else if (cnt == 2) {
-                int2 p0 = sp[s1], p1 = sp[s1 + 1];
-                if (p0.x > p1.x) { const int2 sw = p0; p0 = p1; p1 = sw; sp[s1] = p0; }
-                p1.y |= (int)0x80000000;
-                sp[s1 + 1] = p1;
+            if (cnt == 1 || cnt == 2) {
+                const uint32_t p0 = sp[s1], p1 = sp[s1 + cnt - 1];
+                sp[s1] = min(p0, p1);                // same word twice when cnt == 1 ...
+                sp[s1 + cnt - 1] = max(p0, p1) | LAST; // ... and this store comes second
             }
             const unsigned many = __ballot_sync(0xffffffffu, cnt > 2);
             if (many) {
@@ -404,12 +424,12 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
             const int t = work[w];
             const int e1 = cur[t], s1 = t ? cur[t - 1] : 0;
             for (int i = s1 + 1; i < e1; i++) {
-                const int2 v = sp[i];
+                const uint32_t v = sp[i];
                 int j = i - 1;
-                while (j >= s1 && sp[j].x > v.x) { sp[j + 1] = sp[j]; j--; }
+                while (j >= s1 && sp[j] > v) { sp[j + 1] = sp[j]; j--; }
                 sp[j + 1] = v;
             }
-            sp[e1 - 1].y |= (int)0x80000000;
+            sp[e1 - 1] |= LAST; // 6. last pair of the tile
         }
         __syncthreads();
     } else {
@@ -424,19 +444,22 @@ sym_fill_smem_kernel(const int32_t *__restrict__ rowlist, const int32_t *__restr
                 const int t = prodt[ae.y + i];
                 const int pos = cur[t];
                 cur[t] = pos + 1;
-                sp[pos] = make_int2(a0 + e, ae.x + i);
+                sp[pos] = ((uint32_t)e << FILL_IBITS) | (uint32_t)i;
             }
             __syncthreads();
         }
-    }
-    // 6. mark the last pair of every tile (sign bit of .y): the numeric pass finds tile ends
-    //    in the pair stream itself instead of chasing pair_ptr
-    if (maxcnt) {
-        for (int t = tid; t < T; t += FILL_THREADS) sp[cur[t] - 1].y |= (int)0x80000000;
+        // 6. mark the last pair of every tile: the numeric pass finds tile ends in the pair stream itself
+        for (int t = tid; t < T; t += FILL_THREADS) sp[cur[t] - 1] |= LAST;
         __syncthreads();
     }
-    // 7. stream the row's pairs out
-    for (int x = tid; x < P; x += FILL_THREADS) pairs[pbase + x] = sp[x];
+    tick(6);
+    // 7. stream the row's pairs out as (A tile, B tile | last): 8 bytes per pair, coalesced
+    for (int x = tid; x < P; x += FILL_THREADS) {
+        const uint32_t w = sp[x];
+        const int e = (int)((w >> FILL_IBITS) & (FILL_ACAP - 1));
+        pairs[pbase + x] = make_int2(a0 + e, (aent[e].x + (int)(w & ((1u << FILL_IBITS) - 1u))) | (int)(w & LAST));
+    }
+    tick(7);
 }
 
 // ---- fill, long rows: one CTA per row, every warp owns a range of output tiles -----------------------
@@ -1197,6 +1220,10 @@ __global__ void classify_rows_kernel(int nbr, const int32_t *__restrict__ a_rowp
         else if (mw <= DENSE_M1) cls = 7;
     }
     if (cls == 4 && T <= big_tcap) cls = 8;                  // counters fit in shared memory: per-warp tile ranges
+    if (cls >= 1 && cls <= 3) { // what the class really needs: its launch is sized from these
+        atomicMax(&counts[NCLASS + 2 + (cls - 1)], P);
+        atomicMax(&counts[NCLASS + 5 + (cls - 1)], T);
+    }
     const int slot = atomicAdd(&counts[cls], 1);
     lists[(size_t)cls * nbr + slot] = row;
 }
@@ -1290,12 +1317,13 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     BSP_TRY(sc.alloc(&row_prod, (size_t)nbr + 1));
     BSP_TRY(sc.alloc(&row_prod_ptr, (size_t)nbr + 1));
     BSP_TRY(sc.alloc(&lists, (size_t)NCLASS * (nbr > 0 ? nbr : 1)));
-    BSP_TRY(sc.alloc(&counts, (size_t)NCLASS + 2)); // [NCLASS] = heavy rows of the count pass, [NCLASS+1] = per-row overflow flag
+    BSP_TRY(sc.alloc(&counts, (size_t)NCLASS + 8)); // [NCLASS] = heavy rows of the count pass, [NCLASS+1] = per-row overflow flag,
+                                                    // [NCLASS+2 .. +4] / [NCLASS+5 .. +7] = most products / tiles of a row in classes 1..3
     BSP_TRY(sc.alloc(&heavy, (size_t)(nbr > 0 ? nbr : 1)));
     BSP_TRY(sc.alloc(&out->c_rowptr, (size_t)nbr + 1));
     BSP_CUDA(ctx, cudaMemsetAsync(row_cnt + nbr, 0, sizeof(int32_t), ctx->stream));
     BSP_CUDA(ctx, cudaMemsetAsync(row_prod + nbr, 0, sizeof(int32_t), ctx->stream));
-    BSP_CUDA(ctx, cudaMemsetAsync(counts, 0, (NCLASS + 2) * sizeof(int32_t), ctx->stream));
+    BSP_CUDA(ctx, cudaMemsetAsync(counts, 0, (NCLASS + 8) * sizeof(int32_t), ctx->stream));
 
     int grid = (nbr + SYM_WARPS - 1) / SYM_WARPS;
     const int max_grid = ctx->sm_count * 8;
@@ -1303,8 +1331,10 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     if (grid < 1) grid = 1;
     // capacity classes of the shared-memory fill (tile products / output tiles of a row):
     // about 8 / 2 / 1 CTAs per SM; larger rows use the global-memory variant
-    const int acap = 512;
-    int caps[3] = {1536, 8200, 15000}, tcaps[3] = {1536, 6000, 15000};
+    // (with 4 B per pair in shared memory: three CTAs per SM up to 7680 products / 5632 tiles, two up to 12288 / 8192;
+    // every class is then launched with the capacity its own rows need -- their maxima come back with the totals)
+    const int acap = FILL_ACAP;
+    int caps[3] = {1536, 7680, 12288}, tcaps[3] = {1536, 5632, 8192};
     if (const char *e = getenv("BSP_SYM_CAPS")) { // test hook: force rows into the larger classes
         int a, b, c;
         if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && a <= b && b <= c) {
@@ -1328,6 +1358,7 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     int big_tcap = 0;
     if (8 * (size_t)words + 64 < 110 * 1024) big_tcap = (int)((110 * 1024 - 8 * (size_t)words) / 4) - 8;
     if (const char *e = getenv("BSP_SYM_BIG")) { if (atoi(e) == 0) big_tcap = 0; }
+    if (B->nbc > (1 << FILL_IBITS)) caps[0] = caps[1] = caps[2] = tcaps[0] = tcaps[1] = tcaps[2] = 0; // packed pair: 22-bit offset in a B row
     for (int c = 0; c < 3; c++) {
         if (caps[c] > 60000) caps[c] = 60000; // tile ranks are kept as 16-bit values in shared memory
         if (tcaps[c] > caps[c]) tcaps[c] = caps[c];
@@ -1365,13 +1396,13 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     // store into mapped pinned memory, not a copy -- see bsp_publish
     int32_t *h_nnzb = (int32_t *)ctx->pinned;
     int64_t *h_nprod = (int64_t *)((char *)ctx->pinned + 8);
-    int32_t *h_counts = (int32_t *)((char *)ctx->pinned + 16);
+    int32_t *h_counts = (int32_t *)((char *)ctx->pinned + 128); // clear of the numeric pass's counter at +64
     {
         bsp_publish_list pl = {};
         pl.n = 3;
         pl.src[0] = out->c_rowptr + nbr; pl.offset[0] = 0;  pl.words[0] = 1;
         pl.src[1] = row_prod_ptr + nbr;  pl.offset[1] = 8;  pl.words[1] = 2;
-        pl.src[2] = counts;              pl.offset[2] = 16; pl.words[2] = NCLASS + 2;
+        pl.src[2] = counts;              pl.offset[2] = 128; pl.words[2] = NCLASS + 8;
         BSP_TRY(bsp_publish(ctx, pl));
     }
     bsp_trace_mark(ctx, "sym_scans");
@@ -1380,6 +1411,8 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     out->nprod = *h_nprod;
     int ncls[NCLASS];
     for (int c = 0; c < NCLASS; c++) ncls[c] = h_counts[c];
+    int cmax_p[3], cmax_t[3]; // most tile products / output tiles of a row in each shared-memory class
+    for (int c = 0; c < 3; c++) { cmax_p[c] = h_counts[NCLASS + 2 + c]; cmax_t[c] = h_counts[NCLASS + 5 + c]; }
     if (h_counts[NCLASS + 1])
         BSP_FAIL(ctx, BSP_ERR_LIMIT, "a block row of the product has more than 2^31-1 tile products");
     if (out->nnzb_c < 0) BSP_FAIL(ctx, BSP_ERR_LIMIT, "product has more than 2^31-1 tiles");
@@ -1442,12 +1475,35 @@ int bsp_symbolic(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t row_l
     }
     for (int c = 0; c < 3; c++) {
         if (ncls[c + 1] == 0) continue;
-        const size_t bytes = fill_smem_bytes(words, caps[c], tcaps[c], acap);
-        BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        sym_fill_smem_kernel<<<ncls[c + 1], FILL_THREADS, bytes, ctx->stream>>>(
-            lists + (size_t)(c + 1) * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, caps[c], tcaps[c], acap,
+        // capacity the rows of this class need (even: keeps the arrays behind aligned), not the class bound
+        int pcap = (cmax_p[c] + 65) & ~63, tcap = (cmax_t[c] + 65) & ~63;
+        if (pcap > caps[c] || getenv("BSP_SYM_CAPS")) pcap = caps[c];
+        if (tcap > tcaps[c] || getenv("BSP_SYM_CAPS")) tcap = tcaps[c];
+        if (pcap < 2) pcap = 2;
+        if (tcap < 2) tcap = 2;
+        const size_t bytes = fill_smem_bytes(words, pcap, tcap, acap);
+        const char *spe = getenv("BSP_SYM_PROF");
+        const bool sprof = spe && spe[0] == '1';
+        auto fill_kernel = sprof ? sym_fill_smem_kernel<true> : sym_fill_smem_kernel<false>;
+        BSP_CUDA(ctx, cudaFuncSetAttribute(fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        if (sprof) {
+            unsigned long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            BSP_CUDA(ctx, cudaMemcpyToSymbolAsync(sym_fill_prof, zero, sizeof(zero), 0, cudaMemcpyHostToDevice, ctx->stream));
+        }
+        fill_kernel<<<ncls[c + 1], FILL_THREADS, bytes, ctx->stream>>>(
+            lists + (size_t)(c + 1) * nbr, A->rowptr, A->colidx, B->nbr, B->rowptr, B->colidx, words, pcap, tcap, acap,
             out->c_rowptr, row_prod_ptr, out->c_colidx, out->pair_ptr, out->pairs);
         BSP_LAUNCH_CHECK(ctx);
+        if (sprof) {
+            unsigned long long h[8];
+            BSP_CUDA(ctx, cudaMemcpyFromSymbolAsync(h, sym_fill_prof, sizeof(h), 0, cudaMemcpyDeviceToHost, ctx->stream));
+            BSP_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            static const char *names[8] = {"init+A_entries", "columns+bitmap", "ranks+sorted_cols", "tile_of_product+counts", "scan+pair_ptr",
+                                           "placement", "order+flags", "stream_out"};
+            fprintf(stderr, "[bsp sym prof] class %d: %d rows, smem %zu B, cycles per row:", c + 1, ncls[c + 1], bytes);
+            for (int i = 0; i < 8; i++) fprintf(stderr, " %s=%.0f", names[i], (double)h[i] / ncls[c + 1]);
+            fprintf(stderr, "\n");
+        }
     }
     if (ncls[4] > 0) {
         BSP_CUDA(ctx, cudaFuncSetAttribute(sym_fill_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
