@@ -45,11 +45,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
         "DONE_%=:\n\t"
         "}" ::"r"(bar), "r"(parity) : "memory");
 }
-__device__ __forceinline__ void cp16(uint32_t dst, const void *src)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
-
 // shared-memory matrix descriptor, no swizzle (cute::UMMA::SmemDescriptor): start >> 4,
 // leading byte offset >> 4 at bit 16, stride byte offset >> 4 at bit 32, version 1 at bit 46
 __device__ __forceinline__ uint64_t umma_desc(uint32_t addr, uint32_t lbo, uint32_t sbo)
