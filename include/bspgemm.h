@@ -234,8 +234,8 @@ int bsp_chain_distributed(bsp_ctx *ctx, bsp_comm *comm, bsp_mat *const *mats, in
                           bsp_mat **out, bsp_stats *stats, char *log, size_t log_cap);
 
 /* Contiguous block-row panels of A*B for `nparts` GPUs, balanced by the work of every block row
- * (tile products, from the operands' row pointers, computed on the device): bounds[0..nparts],
- * host array.  Panel p is rows [bounds[p], bounds[p+1]); feed it to bsp_spgemm_panel.  No reference
+ * (tile products, from the operands' row pointers, computed on the device; block rows too long for the
+ * shared-memory classes of the symbolic pass count 40 % more): bounds[0..nparts], host array.  Panel p is rows [bounds[p], bounds[p+1]); feed it to bsp_spgemm_panel.  No reference
  * counterpart (the reference cannot split one product). */
 int bsp_panel_bounds(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t nparts, int32_t *bounds);
 

@@ -144,7 +144,8 @@ __global__ void clamp_rowptr_kernel(int32_t *__restrict__ rp, int n, int32_t s0)
 
 // tile products of every block row of A*B (warp per row): the balance measure of bsp_panel_bounds
 __global__ void row_work_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr, const int32_t *__restrict__ a_colidx,
-                                int b_nbr, const int32_t *__restrict__ b_rowptr, int32_t *__restrict__ work)
+                                int b_nbr, const int32_t *__restrict__ b_rowptr, int long_row, int long_pct,
+                                int32_t *__restrict__ work)
 {
     const int lane = threadIdx.x & 31;
     const int row = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
@@ -158,6 +159,7 @@ __global__ void row_work_kernel(int a_nbr, const int32_t *__restrict__ a_rowptr,
     }
 #pragma unroll
     for (int d = 16; d; d >>= 1) w += __shfl_xor_sync(0xffffffffu, w, d);
+    if (w > long_row) w += w * long_pct / 100; // long rows cost more per tile product in the symbolic pass
     if (lane == 0) work[row] = row < a_nbr ? (int32_t)(w > 0x7fffffffLL ? 0x7fffffffLL : w) : 0;
 }
 
@@ -550,8 +552,14 @@ int bsp_panel_bounds(bsp_ctx *ctx, const bsp_mat *A, const bsp_mat *B, int32_t n
     int64_t *cum = nullptr;
     BSP_TRY(sc.alloc(&work, (size_t)nbr + 1));
     BSP_TRY(sc.alloc(&cum, (size_t)nbr + 1));
+    // Rows above the shared-memory classes of the symbolic pass (one CTA walks the whole row) are charged 40 % more per
+    // tile product (BSP_PANEL_LONG_W overrides).  Measured with tools/rmat_panels_1gpu.py on the R-MAT pattern, max/mean of
+    // the panel times at weights 0 / 20 / 40 / 60 %: 2 panels 1.014 / 1.012 / 1.023 / -, 4 panels 1.067 / 1.030 / 1.008 /
+    // 1.017, 8 panels 1.158 / 1.132 / 1.120 / 1.111.
+    int long_pct = 40;
+    if (const char *e = getenv("BSP_PANEL_LONG_W")) { const int v = atoi(e); if (v >= 0 && v <= 400) long_pct = v; }
     row_work_kernel<<<(unsigned)(((int64_t)(nbr + 1) * 32 + 255) / 256), 256, 0, ctx->stream>>>(nbr, A->rowptr, A->colidx, B->nbr,
-                                                                                                B->rowptr, work);
+                                                                                                B->rowptr, 12288, long_pct, work);
     BSP_LAUNCH_CHECK(ctx);
     BSP_TRY(bsp_scan_i32_to_i64(ctx, work, cum, (int64_t)nbr + 1)); // cum[r] = work of the rows below r
     std::vector<int64_t> h((size_t)nbr + 1);
