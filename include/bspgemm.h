@@ -82,7 +82,8 @@ int bsp_mat_from_coo_f32(bsp_ctx *ctx, int32_t rows, int32_t cols, int32_t k, in
 int bsp_mat_to_coo_f32(bsp_ctx *ctx, const bsp_mat *m, int32_t *brow, int32_t *bcol, float *vals);
 int bsp_mat_is_f32(const bsp_mat *m);
 /* float32 products: 0 = auto (tensor cores -- TF32 inputs, fp32 accumulate -- for k = 32 and 64, fp32 SIMT otherwise),
- * 1 = fp32 SIMT, 2 = tensor cores (k = 32 or 64 only) */
+ * 1 = fp32 SIMT, 2 = tensor cores (k = 32 or 64 only).  The tensor-core path repacks both operands into two scratch
+ * buffers of their size that stay with the context (they only grow) until bsp_ctx_destroy. */
 int bsp_ctx_set_f32_path(bsp_ctx *ctx, int path);
 
 /* Same, from DEVICE memory (arrays are copied, not adopted: the copies are complete on return). */
